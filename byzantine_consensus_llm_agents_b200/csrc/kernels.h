@@ -1,0 +1,39 @@
+// Internal C++ declarations shared by the .cu files; the public C ABI is include/bcg_b200.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/bcg_b200.h"
+
+namespace bcg {
+
+int gemm_bf16_tn(const void* X, const void* W, void* out, int M, int N, int K, long long ldx,
+                 long long ldw, long long ld_out, int epi, int splits, int flags,
+                 cudaStream_t stream);
+int gemm_splits_for(int M, int N, int K);
+
+int embed_rmsnorm(const int* ids, const void* embed, const float* w, float* residual, void* xn,
+                  int T, int d, float eps, cudaStream_t stream);
+int add_rmsnorm(float* residual, const void* delta, int delta_is_f32, int n_partials,
+                long long partial_stride, const float* w, void* xn, const int* src_rows, int T,
+                int d, float eps, cudaStream_t stream);
+int qknorm_rope_kvwrite(const void* qkv, int qkv_is_f32, int n_partials, long long partial_stride,
+                        long long ld_qkv, const float* q_norm_w, const float* k_norm_w,
+                        const float* cos_sin, const int* positions, const int* slot_map,
+                        void* q_out, void* kv_cache, int T, int n_heads, int n_kv_heads,
+                        int page_size, float eps, cudaStream_t stream);
+int swiglu_reduce(const float* partials, int n_partials, long long partial_stride, void* act,
+                  int T, int two_f, cudaStream_t stream);
+
+int decode_attn_paged(const void* q, const void* kv_cache, const int* block_table,
+                      int max_blocks_per_seq, const int* seq_lens, void* out, float* scratch_o,
+                      float* scratch_ml, int B, int n_heads, int n_kv_heads, int page_size,
+                      int max_splits, float scale, cudaStream_t stream);
+int prefill_attn_paged(const void* q, const void* kv_cache, const int* block_table,
+                       int max_blocks_per_seq, const int* tile_info, int n_tiles, void* out,
+                       int n_heads, int n_kv_heads, int page_size, float scale,
+                       cudaStream_t stream);
+
+int mask_sample(const bcg_sampler_args* a, cudaStream_t stream);
+
+}  // namespace bcg

@@ -1,0 +1,135 @@
+// Whole-model prefill / decode steps: the decoder-layer stack of Qwen3 / Mistral
+// (transformers modeling_qwen3.py:305-334 as the arithmetic reference; vLLM
+// models/qwen3.py:216-236 as the op sequence the reference exercises) launched from C++ on
+// one stream, so that one host call = one step and the engine can capture a decode step
+// (plus the sampler) into a single CUDA graph.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace bcg {
+
+#define BCG_TRY(expr)            \
+  do {                           \
+    int _rc = (expr);            \
+    if (_rc != BCG_OK) return _rc; \
+  } while (0)
+
+static int check_model(const bcg_model* m, const bcg_workspace* ws) {
+  if (!m || !ws || m->head_dim != 128 || m->n_layers <= 0 || !m->embed || !m->lm_head ||
+      !m->final_norm || !m->ln1 || !m->ln2 || !m->w_qkv || !m->w_o || !m->w_gate_up ||
+      !m->w_down || !m->kv_cache || !m->cos_sin || !ws->residual || !ws->xn || !ws->q ||
+      !ws->attn || !ws->act || !ws->logits || !ws->xn_last) {
+    set_last_error("bcg_model", "incomplete model / workspace description (head_dim must be 128)");
+    return BCG_ERR_ARG;
+  }
+  return BCG_OK;
+}
+
+int model_prefill(const bcg_model* m, const bcg_workspace* ws, const int* ids, const int* positions,
+                  const int* slot_map, const int* block_table, int max_blocks, const int* tile_info,
+                  int n_tiles, const int* last_rows, int n_seqs, int T, cudaStream_t st) {
+  BCG_TRY(check_model(m, ws));
+  if (T <= 0 || T > ws->T_max || n_seqs <= 0 || n_seqs > ws->B_max || !ws->qkv || !ws->delta) {
+    set_last_error("bcg_model_prefill", "T / n_seqs exceed the workspace");
+    return BCG_ERR_TOO_LARGE;
+  }
+  const int d = m->d_model, hq = m->n_heads, hkv = m->n_kv_heads;
+  const int qkv_dim = (hq + 2 * hkv) * 128;
+  const float scale = 0.08838834764831845f;  // 1/sqrt(128)
+  for (int l = 0; l < m->n_layers; ++l) {
+    if (l == 0) {
+      BCG_TRY(embed_rmsnorm(ids, m->embed, m->ln1[0], ws->residual, ws->xn, T, d, m->rms_eps, st));
+    } else {
+      BCG_TRY(add_rmsnorm(ws->residual, ws->delta, 0, 1, 0, m->ln1[l], ws->xn, nullptr, T, d,
+                          m->rms_eps, st));
+    }
+    BCG_TRY(gemm_bf16_tn(ws->xn, m->w_qkv[l], ws->qkv, T, qkv_dim, d, d, d, qkv_dim, BCG_EPI_BF16, 1,
+                         0, st));
+    BCG_TRY(qknorm_rope_kvwrite(ws->qkv, 0, 1, 0, qkv_dim, m->q_norm ? m->q_norm[l] : nullptr,
+                                m->k_norm ? m->k_norm[l] : nullptr, m->cos_sin, positions, slot_map,
+                                ws->q, m->kv_cache[l], T, hq, hkv, m->page_size, m->rms_eps, st));
+    BCG_TRY(prefill_attn_paged(ws->q, m->kv_cache[l], block_table, max_blocks, tile_info, n_tiles,
+                               ws->attn, hq, hkv, m->page_size, scale, st));
+    BCG_TRY(gemm_bf16_tn(ws->attn, m->w_o[l], ws->delta, T, d, hq * 128, hq * 128, hq * 128, d,
+                         BCG_EPI_BF16, 1, 0, st));
+    BCG_TRY(add_rmsnorm(ws->residual, ws->delta, 0, 1, 0, m->ln2[l], ws->xn, nullptr, T, d,
+                        m->rms_eps, st));
+    BCG_TRY(gemm_bf16_tn(ws->xn, m->w_gate_up[l], ws->act, T, 2 * m->d_ff, d, d, d, m->d_ff,
+                         BCG_EPI_SWIGLU, 1, 0, st));
+    BCG_TRY(gemm_bf16_tn(ws->act, m->w_down[l], ws->delta, T, d, m->d_ff, m->d_ff, m->d_ff, d,
+                         BCG_EPI_BF16, 1, 0, st));
+  }
+  BCG_TRY(add_rmsnorm(ws->residual, ws->delta, 0, 1, 0, m->final_norm, ws->xn_last, last_rows,
+                      n_seqs, d, m->rms_eps, st));
+  BCG_TRY(gemm_bf16_tn(ws->xn_last, m->lm_head, ws->logits, n_seqs, m->vocab, d, d, d, m->vocab,
+                       BCG_EPI_F32, 1, 0, st));
+  return BCG_OK;
+}
+
+int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, const int* positions,
+                 const int* slot_map, const int* seq_lens, const int* block_table, int max_blocks,
+                 int B, int flags, cudaStream_t st) {
+  BCG_TRY(check_model(m, ws));
+  if (B <= 0 || B > ws->B_max || B > 128 || !ws->partials || !ws->attn_scratch_o ||
+      !ws->attn_scratch_ml) {
+    set_last_error("bcg_model_decode", "B exceeds the workspace (or 128), or decode scratch missing");
+    return BCG_ERR_TOO_LARGE;
+  }
+  const int d = m->d_model, hq = m->n_heads, hkv = m->n_kv_heads, ff = m->d_ff;
+  const int qkv_dim = (hq + 2 * hkv) * 128;
+  const float scale = 0.08838834764831845f;
+  const int s_qkv = gemm_splits_for(B, qkv_dim, d);
+  const int s_o = gemm_splits_for(B, d, hq * 128);
+  const int s_gu = gemm_splits_for(B, 2 * ff, d);
+  const int s_dn = gemm_splits_for(B, d, ff);
+  long long need = static_cast<long long>(s_qkv) * B * qkv_dim;
+  const long long n_o = static_cast<long long>(s_o) * B * d;
+  const long long n_gu = s_gu > 1 ? static_cast<long long>(s_gu) * B * 2 * ff : 0;
+  const long long n_dn = static_cast<long long>(s_dn) * B * d;
+  if (n_o > need) need = n_o;
+  if (n_gu > need) need = n_gu;
+  if (n_dn > need) need = n_dn;
+  if (need > ws->partials_floats) {
+    set_last_error("bcg_model_decode", "split-K scratch too small");
+    return BCG_ERR_TOO_LARGE;
+  }
+  const int gf = flags & BCG_GEMM_PDL;
+  float* P = ws->partials;
+  for (int l = 0; l < m->n_layers; ++l) {
+    if (l == 0) {
+      BCG_TRY(embed_rmsnorm(ids, m->embed, m->ln1[0], ws->residual, ws->xn, B, d, m->rms_eps, st));
+    } else {
+      BCG_TRY(add_rmsnorm(ws->residual, P, 1, s_dn, static_cast<long long>(B) * d, m->ln1[l], ws->xn,
+                          nullptr, B, d, m->rms_eps, st));
+    }
+    BCG_TRY(gemm_bf16_tn(ws->xn, m->w_qkv[l], P, B, qkv_dim, d, d, d, qkv_dim, BCG_EPI_F32, s_qkv, gf,
+                         st));
+    BCG_TRY(qknorm_rope_kvwrite(P, 1, s_qkv, static_cast<long long>(B) * qkv_dim, qkv_dim,
+                                m->q_norm ? m->q_norm[l] : nullptr,
+                                m->k_norm ? m->k_norm[l] : nullptr, m->cos_sin, positions, slot_map,
+                                ws->q, m->kv_cache[l], B, hq, hkv, m->page_size, m->rms_eps, st));
+    BCG_TRY(decode_attn_paged(ws->q, m->kv_cache[l], block_table, max_blocks, seq_lens, ws->attn,
+                              ws->attn_scratch_o, ws->attn_scratch_ml, B, hq, hkv, m->page_size,
+                              ws->max_splits, scale, st));
+    BCG_TRY(gemm_bf16_tn(ws->attn, m->w_o[l], P, B, d, hq * 128, hq * 128, hq * 128, d, BCG_EPI_F32,
+                         s_o, gf, st));
+    BCG_TRY(add_rmsnorm(ws->residual, P, 1, s_o, static_cast<long long>(B) * d, m->ln2[l], ws->xn,
+                        nullptr, B, d, m->rms_eps, st));
+    if (s_gu == 1) {
+      BCG_TRY(gemm_bf16_tn(ws->xn, m->w_gate_up[l], ws->act, B, 2 * ff, d, d, d, ff, BCG_EPI_SWIGLU, 1,
+                           gf, st));
+    } else {
+      BCG_TRY(gemm_bf16_tn(ws->xn, m->w_gate_up[l], P, B, 2 * ff, d, d, d, 2 * ff, BCG_EPI_F32, s_gu,
+                           gf, st));
+      BCG_TRY(swiglu_reduce(P, s_gu, static_cast<long long>(B) * 2 * ff, ws->act, B, 2 * ff, st));
+    }
+    BCG_TRY(gemm_bf16_tn(ws->act, m->w_down[l], P, B, d, ff, ff, ff, d, BCG_EPI_F32, s_dn, gf, st));
+  }
+  BCG_TRY(add_rmsnorm(ws->residual, P, 1, s_dn, static_cast<long long>(B) * d, m->final_norm,
+                      ws->xn_last, nullptr, B, d, m->rms_eps, st));
+  BCG_TRY(gemm_bf16_tn(ws->xn_last, m->lm_head, ws->logits, B, m->vocab, d, d, d, m->vocab,
+                       BCG_EPI_F32, 1, gf, st));
+  return BCG_OK;
+}
+
+}  // namespace bcg

@@ -1,0 +1,293 @@
+// Memory-bound glue kernels of the decoder layer:
+//   embed_rmsnorm        K1+K2 : h = E[ids]; xn = rmsnorm(h) * w
+//   add_rmsnorm          K2    : h += delta (bf16, or fp32 split-K partials summed in fixed order);
+//                                xn = rmsnorm(h) * w
+//   qknorm_rope_kvwrite  K4-K6 : per-head RMSNorm of q,k (Qwen3), rotate-half RoPE, q -> bf16,
+//                                k,v -> paged bf16 KV cache
+//   swiglu_reduce        K10   : silu(gate) * up over split-K partials (decode, small models)
+// The residual stream is kept in fp32 (tighter against the fp32 CPU forward that is the
+// oracle); every row is computed independently of the batch it is in (batch-invariant).
+// Arithmetic follows transformers' Qwen3RMSNorm / apply_rotary_pos_emb in fp32
+// (modeling_qwen3.py:50-64,86-148 as cited in SURVEY.md §8c).
+#include "common.cuh"
+#include "kernels.h"
+
+namespace bcg {
+
+constexpr int kNormThreads = 256;
+constexpr int kMaxVecPerThread = 8;  // d <= 256 * 8 * 4 = 8192
+
+__device__ __forceinline__ float block_sum_256(float v, float* red) {
+  v = warp_sum(v);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  float t = 0.f;
+  // fixed order over the 8 warps: deterministic
+#pragma unroll
+  for (int i = 0; i < kNormThreads / 32; ++i) t += red[i];
+  __syncthreads();
+  return t;
+}
+
+__device__ __forceinline__ void store_bf16x4(__nv_bfloat16* p, float a, float b, float c, float d) {
+  uint2 v;
+  v.x = pack_bf16(a, b);
+  v.y = pack_bf16(c, d);
+  *reinterpret_cast<uint2*>(p) = v;
+}
+
+__global__ void __launch_bounds__(kNormThreads)
+embed_rmsnorm_kernel(const int* __restrict__ ids, const __nv_bfloat16* __restrict__ embed,
+                     const float* __restrict__ w, float* __restrict__ residual,
+                     __nv_bfloat16* __restrict__ xn, int d, float eps) {
+  __shared__ float red[kNormThreads / 32];
+  pdl_wait();
+  const int t = blockIdx.x;
+  const long long row = ids[t];
+  const int nvec = d >> 2;
+  float4 x[kMaxVecPerThread];
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < kMaxVecPerThread; ++i) {
+    const int v = threadIdx.x + i * kNormThreads;
+    if (v < nvec) {
+      const uint2 raw = *reinterpret_cast<const uint2*>(embed + row * d + v * 4);
+      x[i] = make_float4(bf16lo(raw.x), bf16hi(raw.x), bf16lo(raw.y), bf16hi(raw.y));
+      ss += x[i].x * x[i].x + x[i].y * x[i].y + x[i].z * x[i].z + x[i].w * x[i].w;
+    }
+  }
+  const float tot = block_sum_256(ss, red);
+  const float inv = rsqrtf(tot / static_cast<float>(d) + eps);
+#pragma unroll
+  for (int i = 0; i < kMaxVecPerThread; ++i) {
+    const int v = threadIdx.x + i * kNormThreads;
+    if (v < nvec) {
+      *reinterpret_cast<float4*>(residual + static_cast<long long>(t) * d + v * 4) = x[i];
+      const float4 ww = *reinterpret_cast<const float4*>(w + v * 4);
+      store_bf16x4(xn + static_cast<long long>(t) * d + v * 4, x[i].x * inv * ww.x,
+                   x[i].y * inv * ww.y, x[i].z * inv * ww.z, x[i].w * inv * ww.w);
+    }
+  }
+  pdl_launch_dependents();
+}
+
+// src_rows == nullptr: in-place residual update over all T rows.
+// src_rows != nullptr: row i reads residual/delta row src_rows[i], writes xn row i only
+//                      (last-token gather in front of lm_head); residual is left untouched.
+__global__ void __launch_bounds__(kNormThreads)
+add_rmsnorm_kernel(float* __restrict__ residual, const void* __restrict__ delta, int delta_is_f32,
+                   int n_partials, long long partial_stride, const float* __restrict__ w,
+                   __nv_bfloat16* __restrict__ xn, const int* __restrict__ src_rows, int d,
+                   float eps) {
+  __shared__ float red[kNormThreads / 32];
+  pdl_wait();
+  const int t = blockIdx.x;
+  const long long src = src_rows ? src_rows[t] : t;
+  const int nvec = d >> 2;
+  float4 x[kMaxVecPerThread];
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < kMaxVecPerThread; ++i) {
+    const int v = threadIdx.x + i * kNormThreads;
+    if (v < nvec) {
+      float4 r = *reinterpret_cast<const float4*>(residual + src * d + v * 4);
+      if (delta) {
+        if (delta_is_f32) {
+          const float* dp = reinterpret_cast<const float*>(delta) + src * d + v * 4;
+          float4 acc = *reinterpret_cast<const float4*>(dp);
+          for (int s = 1; s < n_partials; ++s) {
+            const float4 p = *reinterpret_cast<const float4*>(dp + s * partial_stride);
+            acc.x += p.x; acc.y += p.y; acc.z += p.z; acc.w += p.w;
+          }
+          r.x += acc.x; r.y += acc.y; r.z += acc.z; r.w += acc.w;
+        } else {
+          const uint2 raw = *reinterpret_cast<const uint2*>(
+              reinterpret_cast<const __nv_bfloat16*>(delta) + src * d + v * 4);
+          r.x += bf16lo(raw.x); r.y += bf16hi(raw.x); r.z += bf16lo(raw.y); r.w += bf16hi(raw.y);
+        }
+      }
+      x[i] = r;
+      ss += r.x * r.x + r.y * r.y + r.z * r.z + r.w * r.w;
+    }
+  }
+  const float tot = block_sum_256(ss, red);
+  const float inv = rsqrtf(tot / static_cast<float>(d) + eps);
+#pragma unroll
+  for (int i = 0; i < kMaxVecPerThread; ++i) {
+    const int v = threadIdx.x + i * kNormThreads;
+    if (v < nvec) {
+      if (!src_rows) *reinterpret_cast<float4*>(residual + static_cast<long long>(t) * d + v * 4) = x[i];
+      const float4 ww = *reinterpret_cast<const float4*>(w + v * 4);
+      store_bf16x4(xn + static_cast<long long>(t) * d + v * 4, x[i].x * inv * ww.x,
+                   x[i].y * inv * ww.y, x[i].z * inv * ww.z, x[i].w * inv * ww.w);
+    }
+  }
+  pdl_launch_dependents();
+}
+
+// One warp per (token, head).  head_dim is fixed at 128: lane l owns dims {2l, 2l+1} and
+// {64+2l, 64+2l+1}, i.e. both members of each rotate-half pair.
+// KV cache layout (one layer): [page][2 (k,v)][n_kv_heads][page_size][128] bf16.
+__global__ void __launch_bounds__(128)
+qknorm_rope_kvwrite_kernel(const void* __restrict__ qkv, int qkv_is_f32, int n_partials,
+                           long long partial_stride, long long ld_qkv,
+                           const float* __restrict__ q_norm_w, const float* __restrict__ k_norm_w,
+                           const float* __restrict__ cos_sin, const int* __restrict__ positions,
+                           const int* __restrict__ slot_map, __nv_bfloat16* __restrict__ q_out,
+                           __nv_bfloat16* __restrict__ kv_cache, int T, int n_heads, int n_kv_heads,
+                           int page_size, float eps) {
+  pdl_wait();
+  const int lane = threadIdx.x & 31;
+  const int heads_total = n_heads + 2 * n_kv_heads;
+  const long long wid = static_cast<long long>(blockIdx.x) * 4 + (threadIdx.x >> 5);
+  if (wid < static_cast<long long>(T) * heads_total) {
+    const int t = static_cast<int>(wid / heads_total);
+    const int h = static_cast<int>(wid - static_cast<long long>(t) * heads_total);
+    const long long base = static_cast<long long>(t) * ld_qkv + h * 128;
+    float lo0, lo1, hi0, hi1;
+    if (qkv_is_f32) {
+      const float* p = reinterpret_cast<const float*>(qkv) + base;
+      float2 a = *reinterpret_cast<const float2*>(p + 2 * lane);
+      float2 b = *reinterpret_cast<const float2*>(p + 64 + 2 * lane);
+      for (int s = 1; s < n_partials; ++s) {
+        const float2 a2 = *reinterpret_cast<const float2*>(p + s * partial_stride + 2 * lane);
+        const float2 b2 = *reinterpret_cast<const float2*>(p + s * partial_stride + 64 + 2 * lane);
+        a.x += a2.x; a.y += a2.y; b.x += b2.x; b.y += b2.y;
+      }
+      lo0 = a.x; lo1 = a.y; hi0 = b.x; hi1 = b.y;
+    } else {
+      const __nv_bfloat16* p = reinterpret_cast<const __nv_bfloat16*>(qkv) + base;
+      const uint32_t a = *reinterpret_cast<const uint32_t*>(p + 2 * lane);
+      const uint32_t b = *reinterpret_cast<const uint32_t*>(p + 64 + 2 * lane);
+      lo0 = bf16lo(a); lo1 = bf16hi(a); hi0 = bf16lo(b); hi1 = bf16hi(b);
+    }
+    const bool is_q = h < n_heads;
+    const bool is_k = !is_q && h < n_heads + n_kv_heads;
+    if (is_q || is_k) {
+      const float* nw = is_q ? q_norm_w : k_norm_w;
+      if (nw) {
+        const float ss = warp_sum(lo0 * lo0 + lo1 * lo1 + hi0 * hi0 + hi1 * hi1);
+        const float inv = rsqrtf(ss * (1.0f / 128.0f) + eps);
+        const float2 wl = *reinterpret_cast<const float2*>(nw + 2 * lane);
+        const float2 wh = *reinterpret_cast<const float2*>(nw + 64 + 2 * lane);
+        lo0 = lo0 * inv * wl.x; lo1 = lo1 * inv * wl.y;
+        hi0 = hi0 * inv * wh.x; hi1 = hi1 * inv * wh.y;
+      }
+      const int pos = positions[t];
+      const float2 c = *reinterpret_cast<const float2*>(cos_sin + static_cast<long long>(pos) * 128 + 2 * lane);
+      const float2 s = *reinterpret_cast<const float2*>(cos_sin + static_cast<long long>(pos) * 128 + 64 + 2 * lane);
+      const float r_lo0 = lo0 * c.x - hi0 * s.x;
+      const float r_lo1 = lo1 * c.y - hi1 * s.y;
+      const float r_hi0 = hi0 * c.x + lo0 * s.x;
+      const float r_hi1 = hi1 * c.y + lo1 * s.y;
+      lo0 = r_lo0; lo1 = r_lo1; hi0 = r_hi0; hi1 = r_hi1;
+    }
+    const uint32_t plo = pack_bf16(lo0, lo1), phi = pack_bf16(hi0, hi1);
+    if (is_q) {
+      __nv_bfloat16* o = q_out + (static_cast<long long>(t) * n_heads + h) * 128;
+      *reinterpret_cast<uint32_t*>(o + 2 * lane) = plo;
+      *reinterpret_cast<uint32_t*>(o + 64 + 2 * lane) = phi;
+    } else {
+      const int kvh = is_k ? h - n_heads : h - n_heads - n_kv_heads;
+      const int slot = slot_map[t];
+      if (slot >= 0) {
+        const int page = slot / page_size, off = slot - page * page_size;
+        __nv_bfloat16* o = kv_cache +
+            (((static_cast<long long>(page) * 2 + (is_k ? 0 : 1)) * n_kv_heads + kvh) * page_size + off) * 128;
+        *reinterpret_cast<uint32_t*>(o + 2 * lane) = plo;
+        *reinterpret_cast<uint32_t*>(o + 64 + 2 * lane) = phi;
+      }
+    }
+  }
+  pdl_launch_dependents();
+}
+
+// act[t, f] = silu(gate) * up where the GEMM's N axis is interleaved [16 gate | 16 up].
+__global__ void __launch_bounds__(256)
+swiglu_reduce_kernel(const float* __restrict__ partials, int n_partials, long long partial_stride,
+                     __nv_bfloat16* __restrict__ act, long long total_out, int f) {
+  pdl_wait();
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < total_out) {
+    const long long t = i / f;
+    const int j = static_cast<int>(i - t * f);
+    const long long col = static_cast<long long>(j / 16) * 32 + (j % 16);
+    const float* p = partials + t * (2LL * f) + col;
+    float g = p[0], u = p[16];
+    for (int s = 1; s < n_partials; ++s) {
+      g += p[s * partial_stride];
+      u += p[s * partial_stride + 16];
+    }
+    act[i] = __float2bfloat16_rn(g * (1.0f / (1.0f + __expf(-g))) * u);
+  }
+  pdl_launch_dependents();
+}
+
+// ---------------------------------------------------------------------------------------
+
+int embed_rmsnorm(const int* ids, const void* embed, const float* w, float* residual, void* xn,
+                  int T, int d, float eps, cudaStream_t stream) {
+  if (!ids || !embed || !w || !residual || !xn || T <= 0 || d <= 0 || (d % 4) ||
+      d > kNormThreads * kMaxVecPerThread * 4) {
+    set_last_error("bcg_embed_rmsnorm", "bad argument (d must be a multiple of 4 and <= 8192)");
+    return BCG_ERR_ARG;
+  }
+  embed_rmsnorm_kernel<<<T, kNormThreads, 0, stream>>>(
+      ids, reinterpret_cast<const __nv_bfloat16*>(embed), w, residual,
+      reinterpret_cast<__nv_bfloat16*>(xn), d, eps);
+  BCG_CUDA_CHECK(cudaGetLastError());
+  return BCG_OK;
+}
+
+int add_rmsnorm(float* residual, const void* delta, int delta_is_f32, int n_partials,
+                long long partial_stride, const float* w, void* xn, const int* src_rows, int T,
+                int d, float eps, cudaStream_t stream) {
+  if (!residual || !w || !xn || T <= 0 || d <= 0 || (d % 4) ||
+      d > kNormThreads * kMaxVecPerThread * 4 || n_partials < 1) {
+    set_last_error("bcg_add_rmsnorm", "bad argument (d must be a multiple of 4 and <= 8192)");
+    return BCG_ERR_ARG;
+  }
+  add_rmsnorm_kernel<<<T, kNormThreads, 0, stream>>>(residual, delta, delta_is_f32, n_partials,
+                                                     partial_stride, w,
+                                                     reinterpret_cast<__nv_bfloat16*>(xn), src_rows,
+                                                     d, eps);
+  BCG_CUDA_CHECK(cudaGetLastError());
+  return BCG_OK;
+}
+
+int qknorm_rope_kvwrite(const void* qkv, int qkv_is_f32, int n_partials, long long partial_stride,
+                        long long ld_qkv, const float* q_norm_w, const float* k_norm_w,
+                        const float* cos_sin, const int* positions, const int* slot_map,
+                        void* q_out, void* kv_cache, int T, int n_heads, int n_kv_heads,
+                        int page_size, float eps, cudaStream_t stream) {
+  if (!qkv || !cos_sin || !positions || !slot_map || !q_out || !kv_cache || T <= 0 ||
+      n_heads <= 0 || n_kv_heads <= 0 || page_size <= 0 || n_partials < 1) {
+    set_last_error("bcg_qknorm_rope_kvwrite", "bad argument");
+    return BCG_ERR_ARG;
+  }
+  const long long warps = static_cast<long long>(T) * (n_heads + 2 * n_kv_heads);
+  const unsigned grid = static_cast<unsigned>((warps + 3) / 4);
+  qknorm_rope_kvwrite_kernel<<<grid, 128, 0, stream>>>(
+      qkv, qkv_is_f32, n_partials, partial_stride, ld_qkv, q_norm_w, k_norm_w, cos_sin, positions,
+      slot_map, reinterpret_cast<__nv_bfloat16*>(q_out), reinterpret_cast<__nv_bfloat16*>(kv_cache),
+      T, n_heads, n_kv_heads, page_size, eps);
+  BCG_CUDA_CHECK(cudaGetLastError());
+  return BCG_OK;
+}
+
+int swiglu_reduce(const float* partials, int n_partials, long long partial_stride, void* act,
+                  int T, int two_f, cudaStream_t stream) {
+  if (!partials || !act || T <= 0 || two_f <= 0 || (two_f % 32) || n_partials < 1) {
+    set_last_error("bcg_swiglu_reduce", "bad argument (2F must be a multiple of 32)");
+    return BCG_ERR_ARG;
+  }
+  const int f = two_f / 2;
+  const long long total = static_cast<long long>(T) * f;
+  swiglu_reduce_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(
+      partials, n_partials, partial_stride, reinterpret_cast<__nv_bfloat16*>(act), total, f);
+  BCG_CUDA_CHECK(cudaGetLastError());
+  return BCG_OK;
+}
+
+}  // namespace bcg

@@ -1,0 +1,214 @@
+"""Model descriptions and weight packing for the engine.
+
+Architectures are the ones the reference's MODEL_PRESETS name (config.py:20-25) with the
+dimensions of SURVEY.md §8d.  Weights are random-init (there are no checkpoints offline):
+N(0, 0.02) linears/embeddings, norm weights 1 — transformers' default init — either taken from
+a transformers state_dict (parity tests: same values as the CPU oracle) or generated directly
+on the GPU (bench).  All matrices are bf16; norm weights and the RoPE table are fp32.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+
+import torch
+
+from . import lib as L
+
+
+@dataclass(frozen=True)
+class ModelConfig:
+    name: str
+    n_layers: int
+    d_model: int
+    n_heads: int
+    n_kv_heads: int
+    d_ff: int
+    vocab: int
+    head_dim: int = 128
+    rms_eps: float = 1e-6
+    rope_theta: float = 1e6
+    qk_norm: bool = True          # Qwen3 per-head q/k RMSNorm; Mistral has none
+    tie_embeddings: bool = False
+    family: str = "qwen3"         # chat-template / tokenizer family
+    max_pos: int = 8192
+
+    @property
+    def qkv_dim(self) -> int:
+        return (self.n_heads + 2 * self.n_kv_heads) * self.head_dim
+
+    @property
+    def kv_bytes_per_token(self) -> int:
+        return 2 * self.n_layers * self.n_kv_heads * self.head_dim * 2
+
+    def layer_weight_bytes(self) -> int:
+        d, f = self.d_model, self.d_ff
+        per = self.qkv_dim * d + d * self.n_heads * self.head_dim + 2 * f * d + d * f
+        return 2 * per
+
+    def decode_weight_bytes(self) -> int:
+        """bf16 bytes streamed per decode step: all layer matrices + lm_head (SURVEY §8d col 9)."""
+        return self.n_layers * self.layer_weight_bytes() + 2 * self.vocab * self.d_model
+
+    def prefill_gemm_flops_per_token(self) -> int:
+        return self.n_layers * self.layer_weight_bytes()  # 2 FLOP per bf16 weight = bytes
+
+
+PRESETS = {
+    "qwen3-0.6b": ModelConfig("qwen3-0.6b", 28, 1024, 16, 8, 3072, 151936, tie_embeddings=True),
+    "qwen3-8b": ModelConfig("qwen3-8b", 36, 4096, 32, 8, 12288, 151936),
+    "qwen3-14b": ModelConfig("qwen3-14b", 40, 5120, 40, 8, 17408, 151936),
+    "qwen3-32b": ModelConfig("qwen3-32b", 64, 5120, 64, 8, 25600, 151936),
+    "mistral-22b": ModelConfig("mistral-22b", 56, 6144, 48, 8, 16384, 32768, qk_norm=False,
+                               family="mistral"),
+}
+
+_HF_NAMES = {
+    "qwen/qwen3-0.6b": "qwen3-0.6b",
+    "qwen/qwen3-8b": "qwen3-8b",
+    "qwen/qwen3-14b": "qwen3-14b",
+    "qwen/qwen3-32b": "qwen3-32b",
+    "mistralai/mistral-small-instruct-2409": "mistral-22b",
+}
+
+
+def config_for(model_name: str) -> ModelConfig:
+    key = model_name.lower()
+    if key in PRESETS:
+        return PRESETS[key]
+    if key in _HF_NAMES:
+        return PRESETS[_HF_NAMES[key]]
+    raise KeyError(f"no architecture known for model {model_name!r}")
+
+
+def rope_table(cfg: ModelConfig, device) -> torch.Tensor:
+    """[max_pos, 128] fp32: cos(pos * inv_freq)[0:64] | sin(...)[0:64], computed as transformers
+    does (modeling_qwen3.py Qwen3RotaryEmbedding: inv_freq fp32, outer product fp32)."""
+    dim = cfg.head_dim
+    inv_freq = 1.0 / (cfg.rope_theta ** (torch.arange(0, dim, 2, dtype=torch.int64).float() / dim))
+    pos = torch.arange(cfg.max_pos, dtype=torch.float32)
+    freqs = pos[:, None] * inv_freq[None, :]
+    return torch.cat([freqs.cos(), freqs.sin()], dim=1).contiguous().to(device)
+
+
+def interleave_gate_up(gate: torch.Tensor, up: torch.Tensor) -> torch.Tensor:
+    """[F,d],[F,d] -> [2F,d] with rows laid out [16 gate | 16 up] repeating (GEMM SwiGLU epilogue)."""
+    f, d = gate.shape
+    assert f % 16 == 0
+    return torch.stack([gate.view(f // 16, 16, d), up.view(f // 16, 16, d)], dim=1).reshape(2 * f, d)
+
+
+@dataclass
+class Weights:
+    cfg: ModelConfig
+    embed: torch.Tensor
+    lm_head: torch.Tensor
+    final_norm: torch.Tensor
+    ln1: list = field(default_factory=list)
+    ln2: list = field(default_factory=list)
+    w_qkv: list = field(default_factory=list)
+    w_o: list = field(default_factory=list)
+    w_gate_up: list = field(default_factory=list)
+    w_down: list = field(default_factory=list)
+    q_norm: list = field(default_factory=list)
+    k_norm: list = field(default_factory=list)
+    cos_sin: torch.Tensor = None
+
+    @staticmethod
+    def from_hf_state_dict(cfg: ModelConfig, sd: dict, device) -> "Weights":
+        def bf(t):
+            return t.detach().to(torch.bfloat16).contiguous().to(device)
+
+        def f32(t):
+            return t.detach().float().contiguous().to(device)
+
+        embed = bf(sd["model.embed_tokens.weight"])
+        lm = embed if cfg.tie_embeddings or "lm_head.weight" not in sd else bf(sd["lm_head.weight"])
+        w = Weights(cfg, embed, lm, f32(sd["model.norm.weight"]))
+        for l in range(cfg.n_layers):
+            p = f"model.layers.{l}."
+            w.ln1.append(f32(sd[p + "input_layernorm.weight"]))
+            w.ln2.append(f32(sd[p + "post_attention_layernorm.weight"]))
+            w.w_qkv.append(bf(torch.cat([sd[p + "self_attn.q_proj.weight"],
+                                         sd[p + "self_attn.k_proj.weight"],
+                                         sd[p + "self_attn.v_proj.weight"]], dim=0)))
+            w.w_o.append(bf(sd[p + "self_attn.o_proj.weight"]))
+            w.w_gate_up.append(bf(interleave_gate_up(sd[p + "mlp.gate_proj.weight"],
+                                                     sd[p + "mlp.up_proj.weight"])))
+            w.w_down.append(bf(sd[p + "mlp.down_proj.weight"]))
+            if cfg.qk_norm:
+                w.q_norm.append(f32(sd[p + "self_attn.q_norm.weight"]))
+                w.k_norm.append(f32(sd[p + "self_attn.k_norm.weight"]))
+        w.cos_sin = rope_table(cfg, device)
+        return w
+
+    @staticmethod
+    def random_init(cfg: ModelConfig, device, seed: int = 0) -> "Weights":
+        """transformers-default init generated on the device (bench: 14B would need 59 GB of
+        host fp32 otherwise).  Same distribution, different stream than the CPU oracle."""
+        g = torch.Generator(device=device)
+        g.manual_seed(seed)
+
+        def lin(n, k):
+            t = torch.empty(n, k, dtype=torch.bfloat16, device=device)
+            t.normal_(0.0, 0.02, generator=g)
+            return t
+
+        ones = lambda n: torch.ones(n, dtype=torch.float32, device=device)
+        embed = lin(cfg.vocab, cfg.d_model)
+        lm = embed if cfg.tie_embeddings else lin(cfg.vocab, cfg.d_model)
+        w = Weights(cfg, embed, lm, ones(cfg.d_model))
+        for _ in range(cfg.n_layers):
+            w.ln1.append(ones(cfg.d_model))
+            w.ln2.append(ones(cfg.d_model))
+            w.w_qkv.append(lin(cfg.qkv_dim, cfg.d_model))
+            w.w_o.append(lin(cfg.d_model, cfg.n_heads * cfg.head_dim))
+            w.w_gate_up.append(lin(2 * cfg.d_ff, cfg.d_model))
+            w.w_down.append(lin(cfg.d_model, cfg.d_ff))
+            if cfg.qk_norm:
+                w.q_norm.append(ones(cfg.head_dim))
+                w.k_norm.append(ones(cfg.head_dim))
+        w.cos_sin = rope_table(cfg, device)
+        return w
+
+    def nbytes(self) -> int:
+        seen, total = set(), 0
+        for t in [self.embed, self.lm_head, *self.w_qkv, *self.w_o, *self.w_gate_up, *self.w_down]:
+            if t.data_ptr() not in seen:
+                seen.add(t.data_ptr())
+                total += t.numel() * t.element_size()
+        return total
+
+
+def _ptr_array(tensors):
+    arr = (C.c_void_p * len(tensors))(*[t.data_ptr() for t in tensors])
+    return arr
+
+
+class ModelHandle:
+    """Host-side bcg_model struct (include/bcg_b200.h) pointing at `Weights` + per-layer KV."""
+
+    def __init__(self, w: Weights, kv_cache_layers: list, page_size: int = 16):
+        cfg = w.cfg
+        self.w = w
+        self.kv = kv_cache_layers
+        self._keep = []
+        m = L.Model()
+        m.n_layers, m.d_model, m.n_heads, m.n_kv_heads = cfg.n_layers, cfg.d_model, cfg.n_heads, cfg.n_kv_heads
+        m.head_dim, m.d_ff, m.vocab = cfg.head_dim, cfg.d_ff, cfg.vocab
+        m.rms_eps, m.page_size = cfg.rms_eps, page_size
+        m.embed, m.lm_head, m.final_norm = w.embed.data_ptr(), w.lm_head.data_ptr(), w.final_norm.data_ptr()
+        for name in ("ln1", "ln2", "w_qkv", "w_o", "w_gate_up", "w_down"):
+            arr = _ptr_array(getattr(w, name))
+            self._keep.append(arr)
+            setattr(m, name, C.cast(arr, C.POINTER(C.c_void_p)))
+        if cfg.qk_norm:
+            for name in ("q_norm", "k_norm"):
+                arr = _ptr_array(getattr(w, name))
+                self._keep.append(arr)
+                setattr(m, name, C.cast(arr, C.POINTER(C.c_void_p)))
+        arr = _ptr_array(kv_cache_layers)
+        self._keep.append(arr)
+        m.kv_cache = C.cast(arr, C.POINTER(C.c_void_p))
+        m.cos_sin = w.cos_sin.data_ptr()
+        self.struct = m

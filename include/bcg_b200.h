@@ -1,0 +1,209 @@
+/* bcg_b200.h — C ABI of the B200-native agent-step engine kernels.
+ *
+ * The reference (leorugli/byzantine-consensus-llm-agents) has no FFI of its own: its hot
+ * path is `VLLMAgent.generate_json / batch_generate_json`
+ * (byzantine_consensus_game/vllm_agent.py:294-455), which hands everything to
+ * `vllm.LLM.generate` (vllm_agent.py:195,331,430,502).  The Python class in
+ * byzantine_consensus_llm_agents_b200/vllm_agent.py replaces that module one-for-one; the
+ * functions below are what that class binds (ctypes) in place of the third-party engine's
+ * CUDA ops.  Each entry cites the engine op it stands in for.
+ *
+ * Conventions: plain pointers and sizes only; every pointer is DEVICE memory owned by the
+ * caller unless the comment says host; `stream` is a cudaStream_t passed as void*; no entry
+ * point allocates or frees device memory; return value 0 = ok, otherwise a BCG_ERR_* code
+ * and bcg_last_error() holds a message.  Re-entrant per stream.  sm_100a only.
+ */
+#ifndef BCG_B200_H_
+#define BCG_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BCG_ABI_VERSION 1
+
+/* status codes */
+#define BCG_STATUS_OK 0
+#define BCG_STATUS_ARG 1
+#define BCG_STATUS_CUDA 2
+#define BCG_STATUS_UNSUPPORTED 3
+#define BCG_STATUS_TOO_LARGE 4
+
+/* GEMM epilogues */
+#define BCG_EPI_BF16 0   /* out bf16 [M, ld_out]                                         */
+#define BCG_EPI_F32 1    /* out fp32 [splits][M, ld_out] (split-K partials, or logits)   */
+#define BCG_EPI_SWIGLU 2 /* W rows interleaved [16 gate | 16 up]; out bf16 [M, N/2]      */
+/* GEMM flags */
+#define BCG_GEMM_PDL 1   /* programmatic dependent launch: weights prefetch before the wait */
+
+int bcg_abi_version(void);
+/* Last error message of the calling thread's most recent failing call (host string). */
+const char* bcg_last_error(void);
+
+/* Y[M,N] = X[M,K] · W[N,K]^T, bf16 inputs, fp32 accumulation on tcgen05 tensor cores with
+ * TMEM accumulators and TMA-fed operands.  Stands in for the cuBLAS `F.linear` calls of
+ * qkv_proj / o_proj / gate_up_proj (+ `_C.silu_and_mul`) / down_proj / lm_head
+ * (vLLM model_executor/models/qwen3.py:145-162,216-236).
+ * M <= 128 selects the weight-streaming (swap-AB, optional split-K) decode path.
+ * ldx, ldw, ld_out are row pitches in elements.  splits > 1 requires BCG_EPI_F32 and an
+ * `out` buffer of splits*M*ld_out floats; the consumer sums the partials in index order. */
+int bcg_gemm_bf16_tn(const void* X, const void* W, void* out, int M, int N, int K, long long ldx,
+                     long long ldw, long long ld_out, int epilogue, int splits, int flags,
+                     void* stream);
+/* Split-K factor the engine uses for a decode GEMM of this shape (host helper, no GPU work). */
+int bcg_gemm_splits_for(int M, int N, int K);
+
+/* residual[t,:] = embed[ids[t],:] (fp32); xn[t,:] = rmsnorm(residual[t,:]) * w  (bf16).
+ * Stands in for `F.embedding` + `_C.rms_norm`. */
+int bcg_embed_rmsnorm(const int* ids, const void* embed, const float* w, float* residual, void* xn,
+                      int T, int d, float eps, void* stream);
+
+/* residual += delta; xn = rmsnorm(residual) * w.  delta is bf16 [T,d] (delta_is_f32 = 0) or
+ * n_partials fp32 slabs [T,d] spaced partial_stride floats apart, summed in index order;
+ * delta may be NULL.  If src_rows != NULL, output row i is computed from row src_rows[i] and
+ * residual is not written (last-token gather in front of lm_head).
+ * Stands in for `_C.fused_add_rms_norm`. */
+int bcg_add_rmsnorm(float* residual, const void* delta, int delta_is_f32, int n_partials,
+                    long long partial_stride, const float* w, void* xn, const int* src_rows, int T,
+                    int d, float eps, void* stream);
+
+/* Per-head q/k RMSNorm (weights may be NULL: Mistral), rotate-half RoPE from a
+ * [max_pos][128] fp32 table (cos[0..63] | sin[0..63]), q -> bf16 [T, n_heads*128], k/v ->
+ * paged cache at slot_map[t] (slot = page*page_size + offset; negative = skip).
+ * qkv is bf16 [T, ld_qkv] or fp32 split-K partials.  head_dim is 128.
+ * KV cache layout (one layer): [page][2][n_kv_heads][page_size][128] bf16.
+ * Stands in for `_C.rms_norm` on heads + `_C.rotary_embedding` + `reshape_and_cache_flash`
+ * (SURVEY.md K4-K6). */
+int bcg_qknorm_rope_kvwrite(const void* qkv, int qkv_is_f32, int n_partials,
+                            long long partial_stride, long long ld_qkv, const float* q_norm_w,
+                            const float* k_norm_w, const float* cos_sin, const int* positions,
+                            const int* slot_map, void* q_out, void* kv_cache, int T, int n_heads,
+                            int n_kv_heads, int page_size, float eps, void* stream);
+
+/* act[t, j] = silu(gate) * up summed over fp32 split-K partials of the interleaved gate_up
+ * GEMM (only needed when that GEMM ran with splits > 1).  Stands in for `_C.silu_and_mul`. */
+int bcg_swiglu_reduce(const float* partials, int n_partials, long long partial_stride, void* act,
+                      int T, int two_f, void* stream);
+
+/* One query token per row over the paged KV cache (GQA, head_dim 128, page_size 16).
+ * seq_lens[b] counts the current token.  scratch_o: B*n_heads*max_splits*128 floats,
+ * scratch_ml: B*n_heads*max_splits*2 floats; max_splits >= ceil(max seq_len / 256).
+ * Stands in for the FlashInfer paged decode kernel vLLM dispatches on sm_100. */
+int bcg_decode_attn_paged(const void* q, const void* kv_cache, const int* block_table,
+                          int max_blocks_per_seq, const int* seq_lens, void* out, float* scratch_o,
+                          float* scratch_ml, int B, int n_heads, int n_kv_heads, int page_size,
+                          int max_splits, float scale, void* stream);
+
+/* Causal attention of ragged new-token rows against cached prefix + new tokens, both read
+ * through the block table.  tile_info: int32 [n_tiles][4] = {sequence, first q row, position
+ * of that row in its sequence, rows (<= 64)}.
+ * Stands in for the FlashInfer paged prefill kernel. */
+int bcg_prefill_attn_paged(const void* q, const void* kv_cache, const int* block_table,
+                           int max_blocks_per_seq, const int* tile_info, int n_tiles, void* out,
+                           int n_heads, int n_kv_heads, int page_size, float scale, void* stream);
+
+/* Grammar-constrained sampler + per-row decode bookkeeping, one thread-block cluster per row.
+ * Applies the JSON-schema token bitmask of the row's DFA state, then greedy argmax
+ * (temperature < 1e-5) or temperature sampling as an exponential race
+ * argmax_i(logit_i / T - log(q_i)), q_i = -log(u_i), u_i from Philox4x32-10(seed[b]; i, step),
+ * with a reproducible fp32 log (see oracle/sampler.py); advances the DFA over the token's
+ * bytes; appends the token; updates next_ids / positions / seq_lens / slot_map so the next
+ * decode step needs no host round-trip.
+ * Stands in for xgrammar `apply_token_bitmask_inplace` + vLLM `Sampler` + the scheduler's
+ * accept_token/stop bookkeeping (vllm v1/sample/sampler.py:91,223-297,
+ * v1/sample/ops/topk_topp_sampler.py:395-416, v1/structured_output/backend_xgrammar.py:148-192). */
+typedef struct bcg_sampler_args {
+  const float* logits;     /* [B, ld_logits] */
+  long long ld_logits;
+  int B;
+  int V;                   /* multiple of 4 */
+  int mask_words;          /* int32 words per mask row = ceil(V/32) */
+  int max_steps;           /* row pitch of out_tokens / chosen / forced */
+  int eos_id0, eos_id1;    /* stop ids (-1 = unused) */
+  int page_size;
+  int max_blocks_per_seq;
+  /* grammar tables */
+  const int* grammar_id;              /* [B], -1 = unconstrained */
+  const int32_t* const* mask_tables;  /* [n_grammars] -> int32 [n_states][mask_words], bit=1 allowed, LSB first */
+  const int16_t* const* trans_tables; /* [n_grammars] -> int16 [n_states][256], -1 = reject */
+  const uint8_t* tok_bytes;           /* concatenated token byte strings */
+  const int* tok_offsets;             /* [V+1] */
+  /* per-row sampling state */
+  const float* temperature;  /* [B] */
+  const uint32_t* seed;      /* [B][2] */
+  const int* max_tokens;     /* [B] */
+  const int* forced;         /* [B, max_steps] teacher-forced ids (<0 = none) or NULL */
+  int* state;                /* [B] DFA state, in/out */
+  int* n_out;                /* [B] tokens emitted so far, in/out */
+  int* finished;             /* [B] in/out: 0 running, 1 eos, 2 length, 3 grammar dead end */
+  int* out_tokens;           /* [B, max_steps] accepted tokens */
+  int* chosen;               /* [B, max_steps] the sampler's own pick (== out_tokens unless forced) or NULL */
+  /* decode bookkeeping */
+  int* next_ids;             /* [B] */
+  int* positions;            /* [B] */
+  int* seq_lens;             /* [B] */
+  int* slot_map;             /* [B] */
+  const int* block_table;    /* [B, max_blocks_per_seq] */
+  int* n_active;             /* [1] number of unfinished rows after this call, or NULL */
+} bcg_sampler_args;
+
+int bcg_mask_sample(const bcg_sampler_args* args /* host struct */, void* stream);
+
+/* Whole-model steps: the layer stack launched from C++ on one stream so a decode step is one
+ * host call (captured into a CUDA graph by the engine).  See DESIGN.md §4. */
+typedef struct bcg_model {
+  int n_layers, d_model, n_heads, n_kv_heads, head_dim, d_ff, vocab;
+  float rms_eps;
+  int page_size;
+  const void* embed;             /* bf16 [vocab, d_model] */
+  const void* lm_head;           /* bf16 [vocab, d_model] */
+  const float* final_norm;       /* [d_model] */
+  const float* const* ln1;       /* host array [n_layers] of device [d_model] */
+  const float* const* ln2;
+  const void* const* w_qkv;      /* bf16 [(n_heads+2*n_kv_heads)*128, d_model] */
+  const void* const* w_o;        /* bf16 [d_model, n_heads*128] */
+  const void* const* w_gate_up;  /* bf16 [2*d_ff, d_model], rows interleaved 16 gate / 16 up */
+  const void* const* w_down;     /* bf16 [d_model, d_ff] */
+  const float* const* q_norm;    /* [128] per layer or NULL array (Mistral) */
+  const float* const* k_norm;
+  void* const* kv_cache;         /* per-layer cache base */
+  const float* cos_sin;          /* [max_pos][128] */
+} bcg_model;
+
+typedef struct bcg_workspace {
+  float* residual;    /* [T_max, d_model] */
+  void* xn;           /* bf16 [T_max, d_model] */
+  void* qkv;          /* bf16 [T_max, qkv_dim]   (prefill)  */
+  void* q;            /* bf16 [T_max, n_heads*128] */
+  void* attn;         /* bf16 [T_max, n_heads*128] */
+  void* act;          /* bf16 [T_max, d_ff] */
+  void* delta;        /* bf16 [T_max, d_model]   (prefill)  */
+  float* partials;    /* fp32 split-K scratch, partials_floats long (decode) */
+  long long partials_floats;
+  float* attn_scratch_o;
+  float* attn_scratch_ml;
+  int max_splits;
+  float* logits;      /* fp32 [B_max, vocab] */
+  void* xn_last;      /* bf16 [B_max, d_model] */
+  int T_max, B_max;
+} bcg_workspace;
+
+/* T new tokens (ragged over sequences) -> KV cache filled, logits of each sequence's last
+ * token in ws->logits[0..n_seqs).  last_rows: device int32 [n_seqs]. */
+int bcg_model_prefill(const bcg_model* m, const bcg_workspace* ws, const int* ids,
+                      const int* positions, const int* slot_map, const int* block_table,
+                      int max_blocks_per_seq, const int* tile_info, int n_tiles,
+                      const int* last_rows, int n_seqs, int T, void* stream);
+/* One decode step for B rows: ids/positions/slot_map/seq_lens are the arrays bcg_mask_sample
+ * maintains; logits land in ws->logits[0..B). */
+int bcg_model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids,
+                     const int* positions, const int* slot_map, const int* seq_lens,
+                     const int* block_table, int max_blocks_per_seq, int B, int flags,
+                     void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BCG_B200_H_ */
