@@ -1,0 +1,253 @@
+"""Deterministic synthetic tokenizer.
+
+The reference lets vLLM load the HuggingFace tokenizer of the model it names
+(vllm_agent.py:126-144); no tokenizer files exist offline, so the engine — and the CPU oracle,
+which imports this same class — use a synthetic byte-level BPE with the real models' id-space
+geometry:
+
+  * ids [0, 256)            the 256 byte tokens (GPT-2 byte<->unicode alphabet, sorted)
+  * ids [256, 256+M)        BPE merges trained on the reference's own prompts
+                            (assets/bpe_merges.json, oracle/tools/make_tokenizer_assets.py)
+  * ids up to n_regular     deterministic filler tokens (never produced by encode(), but
+                            decodable and visible to the grammar mask): words, digits,
+                            punctuation/JSON fragments, whitespace runs, UTF-8 characters and
+                            partial UTF-8 sequences — so masks have realistic density and tokens
+                            straddle grammar boundaries
+  * qwen3 family:  26 special tokens at n_regular.. with <|endoftext|>, <|im_start|>,
+                   <|im_end|> first (151643/4/5 at the full 151,936 vocabulary); ids above the
+                   last special token up to the model's vocab are unused padding, as in Qwen.
+  * mistral family: control tokens <unk> <s> </s> [INST] [/INST] ... at ids 0..9.
+
+Encoding uses the `tokenizers` library's BPE model (the same library vLLM uses for HF
+tokenizers); decoding concatenates token bytes, drops special tokens, and decodes UTF-8 with
+replacement, like `skip_special_tokens=True`.
+"""
+from __future__ import annotations
+
+import json
+import random
+from functools import lru_cache
+from pathlib import Path
+
+import numpy as np
+
+ASSETS = Path(__file__).resolve().parent / "assets"
+
+QWEN_SPECIALS = [
+    "<|endoftext|>", "<|im_start|>", "<|im_end|>", "<|object_ref_start|>", "<|object_ref_end|>",
+    "<|box_start|>", "<|box_end|>", "<|quad_start|>", "<|quad_end|>", "<|vision_start|>",
+    "<|vision_end|>", "<|vision_pad|>", "<|image_pad|>", "<|video_pad|>", "<tool_call>",
+    "</tool_call>", "<|fim_prefix|>", "<|fim_middle|>", "<|fim_suffix|>", "<|fim_pad|>",
+    "<|repo_name|>", "<|file_sep|>", "<tool_response>", "</tool_response>", "<think>", "</think>",
+]
+QWEN_RESERVED_TOP = 151936 - 151643  # specials + unused ids at the top of the id space
+
+MISTRAL_SPECIALS = ["<unk>", "<s>", "</s>", "[INST]", "[/INST]", "[TOOL_CALLS]",
+                    "[AVAILABLE_TOOLS]", "[/AVAILABLE_TOOLS]", "[TOOL_RESULTS]", "[/TOOL_RESULTS]"]
+
+
+def _bytes_to_unicode():
+    """GPT-2 byte <-> printable unicode map (the ByteLevel alphabet)."""
+    bs = list(range(ord("!"), ord("~") + 1)) + list(range(0xA1, 0xAD)) + list(range(0xAE, 0x100))
+    cs = bs[:]
+    n = 0
+    for b in range(256):
+        if b not in bs:
+            bs.append(b)
+            cs.append(256 + n)
+            n += 1
+    return dict(zip(bs, map(chr, cs)))
+
+
+_B2U = _bytes_to_unicode()
+_U2B = {u: b for b, u in _B2U.items()}
+
+_WORDS = ("the of and to in is that for it as was with be by on not he this are or his from at "
+          "which but have an had they you were their one all we can her has there been if more "
+          "when will would who so no value round agent consensus propose vote stop continue "
+          "strategy reasoning network honest byzantine agree majority median average trust "
+          "converge history current initial final decision public internal abstain").split()
+
+
+def _filler_tokens(n: int, taken: set) -> list:
+    """n distinct byte strings not in `taken`, from a fixed-seed stdlib PRNG."""
+    rng = random.Random(0xBC6B200)
+    letters = "abcdefghijklmnopqrstuvwxyz"
+    punct = list("{}[]():;,.!?\"'\\/-_=+*&^%$#@~`|<>")
+    json_frags = ['":', '",', '"}', '{"', '":"', '", "', '": "', '"}\n', '":{', '"]', '["', '},', '}}',
+                  '" ', ' "', '\\"', '\\n', '\\\\', '": ', ',"', '" :', '"\n', '\n"', '",\n', '" }']
+    out, seen = [], set(taken)
+
+    def push(b: bytes):
+        if b and b not in seen and len(b) <= 24:
+            seen.add(b)
+            out.append(b)
+
+    for f in json_frags:
+        push(f.encode())
+    for w in _WORDS:
+        for v in (w, " " + w, w.capitalize(), " " + w.capitalize(), w.upper()):
+            push(v.encode())
+    for k in range(2, 17):
+        push(b" " * k)
+        push(b"\n" * min(k, 8))
+        push(b"\t" * min(k, 4))
+    for d in range(1000):
+        push(str(d).encode())
+        push((" " + str(d)).encode())
+    guard = 0
+    while len(out) < n:
+        guard += 1
+        if guard > 50 * n + 100000:
+            raise RuntimeError("filler generation stalled")
+        r = rng.random()
+        if r < 0.50:      # word-like
+            s = "".join(rng.choice(letters) for _ in range(rng.randint(2, 9)))
+            if rng.random() < 0.15:
+                s = s.capitalize()
+            if rng.random() < 0.45:
+                s = " " + s
+            push(s.encode())
+        elif r < 0.60:    # two words / word + punctuation
+            s = rng.choice(_WORDS) + rng.choice([" ", ",", ".", ":", "_", "-"]) + \
+                "".join(rng.choice(letters) for _ in range(rng.randint(1, 5)))
+            push(s.encode())
+        elif r < 0.68:    # punctuation runs, JSON-ish glue
+            s = "".join(rng.choice(punct) for _ in range(rng.randint(1, 3)))
+            if rng.random() < 0.3:
+                s += rng.choice(["\n", " ", "  "])
+            push(s.encode())
+        elif r < 0.74:    # digits
+            s = "".join(rng.choice("0123456789") for _ in range(rng.randint(1, 6)))
+            if rng.random() < 0.3:
+                s = rng.choice([" ", ".", ",", "-"]) + s
+            push(s.encode())
+        elif r < 0.94:    # whole non-ASCII characters (1..3 of them)
+            cps = []
+            for _ in range(rng.randint(1, 3)):
+                lo, hi = rng.choice([(0xA1, 0x24F), (0x370, 0x3FF), (0x400, 0x4FF), (0x4E00, 0x9FFF),
+                                     (0x3040, 0x30FF), (0xAC00, 0xD7A3), (0x1F300, 0x1F64F)])
+                cps.append(chr(rng.randint(lo, hi)))
+            push("".join(cps).encode("utf-8"))
+        else:             # partial UTF-8 sequences (byte-level BPE really has these)
+            ch = chr(rng.randint(0x800, 0xFFFF) if rng.random() < 0.7 else rng.randint(0x10000, 0x1FFFF))
+            if 0xD800 <= ord(ch) <= 0xDFFF:
+                continue
+            b = ch.encode("utf-8")
+            cut = rng.randint(1, len(b) - 1)
+            push(b[:cut] if rng.random() < 0.5 else b[cut:])
+    return out[:n]
+
+
+class SyntheticTokenizer:
+    def __init__(self, family: str = "qwen3", vocab_size: int = 151936):
+        from tokenizers import AddedToken, Tokenizer, decoders, models, pre_tokenizers
+
+        self.family = family
+        self.vocab_size = vocab_size
+        merges = [tuple(m) for m in json.loads((ASSETS / "bpe_merges.json").read_text())]
+        if family == "mistral":
+            specials = MISTRAL_SPECIALS
+            base = len(specials)
+            n_regular = vocab_size - base
+        else:
+            specials = QWEN_SPECIALS
+            base = 0
+            n_regular = vocab_size - QWEN_RESERVED_TOP
+        if n_regular < 256 + 64:
+            raise ValueError("vocab_size too small for the synthetic tokenizer")
+
+        alphabet = sorted(_B2U.values())
+        strs = list(alphabet)
+        have = set(strs)
+        kept_merges = []
+        for a, b in merges:
+            if len(strs) >= min(n_regular, 256 + len(merges)):
+                break
+            if a in have and b in have and (a + b) not in have:
+                kept_merges.append((a, b))
+                strs.append(a + b)
+                have.add(a + b)
+        taken = {bytes(_U2B[c] for c in s) for s in strs}
+        for b in _filler_tokens(n_regular - len(strs), taken):
+            strs.append("".join(_B2U[x] for x in b))
+        assert len(strs) == n_regular and len(set(strs)) == n_regular
+
+        vocab = {}
+        if family == "mistral":
+            for i, s in enumerate(specials):
+                vocab[s] = i
+        for i, s in enumerate(strs):
+            vocab[s] = base + i
+        tok = Tokenizer(models.BPE(vocab=vocab, merges=kept_merges))
+        tok.pre_tokenizer = pre_tokenizers.ByteLevel(add_prefix_space=False, use_regex=True)
+        tok.decoder = decoders.ByteLevel()
+        tok.add_special_tokens([AddedToken(s, special=True, normalized=False) for s in specials])
+        self._tok = tok
+
+        # id -> bytes table (special / unused ids are byte-less)
+        self.token_bytes = [b""] * vocab_size
+        for i, s in enumerate(strs):
+            self.token_bytes[base + i] = bytes(_U2B[c] for c in s)
+        if family == "mistral":
+            self.special_ids = {s: i for i, s in enumerate(specials)}
+            self.bos_id, self.eos_id = self.special_ids["<s>"], self.special_ids["</s>"]
+            self.stop_ids = (self.eos_id,)
+        else:
+            self.special_ids = {s: n_regular + i for i, s in enumerate(specials)}
+            for s, i in self.special_ids.items():
+                assert tok.token_to_id(s) == i, (s, i, tok.token_to_id(s))
+            self.bos_id = None
+            self.eos_id = self.special_ids["<|im_end|>"]
+            self.stop_ids = (self.eos_id, self.special_ids["<|endoftext|>"])
+        self.n_regular = n_regular
+        self.regular_range = (base, base + n_regular)
+        self._is_special = np.zeros(vocab_size, bool)
+        self._is_special[list(self.special_ids.values())] = True
+
+    # ---- encode / decode ---------------------------------------------------------------
+    def encode(self, text: str, add_special_tokens: bool = True) -> list:
+        ids = self._tok.encode(text, add_special_tokens=False).ids
+        if add_special_tokens and self.bos_id is not None:
+            ids = [self.bos_id] + ids
+        return ids
+
+    def decode(self, ids, skip_special_tokens: bool = True) -> str:
+        parts = []
+        for i in ids:
+            i = int(i)
+            if 0 <= i < self.vocab_size:
+                if self._is_special[i]:
+                    if not skip_special_tokens:
+                        parts.append(next(s for s, j in self.special_ids.items() if j == i).encode())
+                else:
+                    parts.append(self.token_bytes[i])
+        return b"".join(parts).decode("utf-8", errors="replace")
+
+    # ---- tables for the grammar compiler / sampler kernel -------------------------------
+    def byte_table(self):
+        """(uint8 blob, int32 offsets[V+1]) of all token byte strings."""
+        lens = np.fromiter((len(b) for b in self.token_bytes), dtype=np.int64, count=self.vocab_size)
+        offsets = np.zeros(self.vocab_size + 1, np.int32)
+        offsets[1:] = np.cumsum(lens)
+        blob = np.frombuffer(b"".join(self.token_bytes), dtype=np.uint8).copy()
+        return blob, offsets
+
+    def encoded_vocab_for_xgrammar(self):
+        """Token strings in the byte-level alphabet, as xgrammar.TokenizerInfo expects for
+        VocabType.BYTE_LEVEL (oracle only)."""
+        out = []
+        inv = {i: s for s, i in self.special_ids.items()}
+        for i in range(self.vocab_size):
+            if i in inv:
+                out.append(inv[i])
+            elif self.token_bytes[i]:
+                out.append("".join(_B2U[b] for b in self.token_bytes[i]))
+            else:
+                out.append(f"<|unused_{i}|>")
+        return out
+
+
+@lru_cache(maxsize=8)
+def get_tokenizer(family: str = "qwen3", vocab_size: int = 151936) -> SyntheticTokenizer:
+    return SyntheticTokenizer(family, vocab_size)
