@@ -40,26 +40,27 @@ int model_prefill(const bcg_model* m, const bcg_workspace* ws, const int* ids, c
     if (l == 0) {
       BCG_TRY(embed_rmsnorm(ids, m->embed, m->ln1[0], ws->residual, ws->xn, T, d, m->rms_eps, st));
     } else {
-      BCG_TRY(add_rmsnorm(ws->residual, ws->delta, 0, 1, 0, m->ln1[l], ws->xn, nullptr, T, d,
+      BCG_TRY(add_rmsnorm(ws->residual, ws->delta, 1, 1, 0, m->ln1[l], ws->xn, nullptr, T, d,
                           m->rms_eps, st));
     }
-    BCG_TRY(gemm_bf16_tn(ws->xn, m->w_qkv[l], ws->qkv, T, qkv_dim, d, d, d, qkv_dim, BCG_EPI_BF16, 1,
+    // projections that feed fp32 consumers keep their fp32 accumulators (no bf16 round trip)
+    BCG_TRY(gemm_bf16_tn(ws->xn, m->w_qkv[l], ws->qkv, T, qkv_dim, d, d, d, qkv_dim, BCG_EPI_F32, 1,
                          0, st));
-    BCG_TRY(qknorm_rope_kvwrite(ws->qkv, 0, 1, 0, qkv_dim, m->q_norm ? m->q_norm[l] : nullptr,
+    BCG_TRY(qknorm_rope_kvwrite(ws->qkv, 1, 1, 0, qkv_dim, m->q_norm ? m->q_norm[l] : nullptr,
                                 m->k_norm ? m->k_norm[l] : nullptr, m->cos_sin, positions, slot_map,
                                 ws->q, m->kv_cache[l], T, hq, hkv, m->page_size, m->rms_eps, st));
     BCG_TRY(prefill_attn_paged(ws->q, m->kv_cache[l], block_table, max_blocks, tile_info, n_tiles,
                                ws->attn, hq, hkv, m->page_size, scale, st));
     BCG_TRY(gemm_bf16_tn(ws->attn, m->w_o[l], ws->delta, T, d, hq * 128, hq * 128, hq * 128, d,
-                         BCG_EPI_BF16, 1, 0, st));
-    BCG_TRY(add_rmsnorm(ws->residual, ws->delta, 0, 1, 0, m->ln2[l], ws->xn, nullptr, T, d,
+                         BCG_EPI_F32, 1, 0, st));
+    BCG_TRY(add_rmsnorm(ws->residual, ws->delta, 1, 1, 0, m->ln2[l], ws->xn, nullptr, T, d,
                         m->rms_eps, st));
     BCG_TRY(gemm_bf16_tn(ws->xn, m->w_gate_up[l], ws->act, T, 2 * m->d_ff, d, d, d, m->d_ff,
                          BCG_EPI_SWIGLU, 1, 0, st));
     BCG_TRY(gemm_bf16_tn(ws->act, m->w_down[l], ws->delta, T, d, m->d_ff, m->d_ff, m->d_ff, d,
-                         BCG_EPI_BF16, 1, 0, st));
+                         BCG_EPI_F32, 1, 0, st));
   }
-  BCG_TRY(add_rmsnorm(ws->residual, ws->delta, 0, 1, 0, m->final_norm, ws->xn_last, last_rows,
+  BCG_TRY(add_rmsnorm(ws->residual, ws->delta, 1, 1, 0, m->final_norm, ws->xn_last, last_rows,
                       n_seqs, d, m->rms_eps, st));
   BCG_TRY(gemm_bf16_tn(ws->xn_last, m->lm_head, ws->logits, n_seqs, m->vocab, d, d, d, m->vocab,
                        BCG_EPI_F32, 1, 0, st));

@@ -172,8 +172,8 @@ class Engine:
         pf = max(splits[0] * B * cfg.qkv_dim, splits[1] * B * d,
                  (splits[2] * B * 2 * cfg.d_ff) if splits[2] > 1 else 0, splits[3] * B * d)
         self.buf = dict(
-            residual=z(T, d, dt=f32), xn=z(T, d), qkv=z(T, cfg.qkv_dim), q=z(T, cfg.n_heads * 128),
-            attn=z(T, cfg.n_heads * 128), act=z(T, cfg.d_ff), delta=z(T, d), partials=z(pf, dt=f32),
+            residual=z(T, d, dt=f32), xn=z(T, d), qkv=z(T, cfg.qkv_dim, dt=f32), q=z(T, cfg.n_heads * 128),
+            attn=z(T, cfg.n_heads * 128), act=z(T, cfg.d_ff), delta=z(T, d, dt=f32), partials=z(pf, dt=f32),
             so=z(B * cfg.n_heads * self.max_splits_cap * 128, dt=f32),
             sml=z(B * cfg.n_heads * self.max_splits_cap * 2, dt=f32),
             logits=z(B, cfg.vocab, dt=f32), xn_last=z(B, d))
@@ -222,7 +222,7 @@ class Engine:
         self._graphs: Dict[tuple, torch.cuda.CUDAGraph] = {}
         self.stats = dict(calls=0, prompts=0, prompt_tokens=0, cached_tokens=0, prefill_tokens=0,
                           decode_steps=0, generated_tokens=0, prefill_s=0.0, decode_s=0.0, host_s=0.0,
-                          gpu_launches=0)
+                          gpu_launches=0, h2d_bytes=0, d2h_bytes=0)
         self._capture_stream = torch.cuda.Stream(self.dev)
         # parity tests: when set to a list, the logits of every step are appended (forces the
         # eager, graph-less decode loop)
@@ -380,12 +380,14 @@ class Engine:
             r[k][:B].copy_(torch.from_numpy(v), non_blocking=False)
         r["seed"][:B].copy_(torch.from_numpy(seeds.view(np.int32)))
         r["block_table"][:B].copy_(torch.from_numpy(bt))
+        self.stats["h2d_bytes"] += sum(v.nbytes for v in host_rows.values()) + seeds.nbytes + bt.nbytes
         if use_forced:
             f = np.full((B, self.max_steps), -1, np.int32)
             for b, q in enumerate(reqs):
                 if q.forced is not None:
                     f[b, :len(q.forced)] = np.asarray(q.forced, np.int32)
             r["forced"][:B].copy_(torch.from_numpy(f))
+            self.stats["h2d_bytes"] += f.nbytes
 
         # ---- prefill in groups of <= T_max new tokens
         ev0, ev1, ev2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
@@ -444,6 +446,7 @@ class Engine:
                 self.n_active_host.copy_(r["n_active"], non_blocking=True)
                 torch.cuda.current_stream().synchronize()
                 done = int(self.n_active_host[0]) == 0
+                self.stats["d2h_bytes"] += 4
         ev2.record()
         torch.cuda.synchronize()
         t_host1 = time.perf_counter()
@@ -452,6 +455,7 @@ class Engine:
         width = int(n_out.max()) if B else 0
         toks = r["out_tokens"][:B, :width].cpu().numpy()
         chosen = r["chosen"][:B, :width].cpu().numpy()
+        self.stats["d2h_bytes"] += n_out.nbytes + fin.nbytes + toks.nbytes + chosen.nbytes
         results = []
         stop = set(self.tk.stop_ids)
         for b in range(B):
@@ -489,6 +493,7 @@ class Engine:
         t = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.int32)).to(dev)
         d_ids, d_pos, d_slots = t(ids), t(np.concatenate(pos)), t(np.concatenate(slots))
         d_tiles, d_last, d_bt = t(np.array(tiles)), t(last), t(bt[b0:b1])
+        self.stats["h2d_bytes"] += sum(x.numel() * 4 for x in (d_ids, d_pos, d_slots, d_tiles, d_last, d_bt))
         # this group's last-token logits go straight to rows b0..b1 of the row-indexed buffer
         base = self.buf["logits"].data_ptr()
         self.ws.logits = base + b0 * cfg.vocab * 4

@@ -175,11 +175,11 @@ typedef struct bcg_model {
 typedef struct bcg_workspace {
   float* residual;    /* [T_max, d_model] */
   void* xn;           /* bf16 [T_max, d_model] */
-  void* qkv;          /* bf16 [T_max, qkv_dim]   (prefill)  */
+  float* qkv;         /* fp32 [T_max, qkv_dim]   (prefill)  */
   void* q;            /* bf16 [T_max, n_heads*128] */
   void* attn;         /* bf16 [T_max, n_heads*128] */
   void* act;          /* bf16 [T_max, d_ff] */
-  void* delta;        /* bf16 [T_max, d_model]   (prefill)  */
+  float* delta;       /* fp32 [T_max, d_model]   (prefill)  */
   float* partials;    /* fp32 split-K scratch, partials_floats long (decode) */
   long long partials_floats;
   float* attn_scratch_o;

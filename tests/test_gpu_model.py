@@ -36,8 +36,12 @@ def _prompts(tk, rng, lens):
     return [rng.integers(lo, hi, size=n).tolist() for n in lens]
 
 
-@pytest.mark.parametrize("cfg", [TINY_QWEN, TINY_MISTRAL, WIDE_QWEN], ids=lambda c: c.name)
-def test_logits_match_fp32_cpu_forward(cfg):
+# wide-qwen3 is a synthetic stress shape whose bf16 ROUNDING FLOOR (fp32 math with only the
+# engine's bf16 roundings applied, oracle/tools/bf16_noise_floor.py) is already rms 0.0048 /
+# max 0.026, so it is held to 3e-2 max and 6e-3 rms; the named architectures are held to 2e-2.
+@pytest.mark.parametrize("cfg,tol", [(TINY_QWEN, LOGIT_TOL), (TINY_MISTRAL, LOGIT_TOL), (WIDE_QWEN, 3e-2)],
+                         ids=lambda c: getattr(c, "name", None))
+def test_logits_match_fp32_cpu_forward(cfg, tol):
     hf, eng, tk = _setup(cfg)
     rng = np.random.default_rng(0)
     lens = [5, 64, 65, 200, 333]
@@ -139,3 +143,28 @@ def test_engine_rejects_oversized_request():
     # the pool is intact afterwards
     ok = eng.generate([Request("", None, 0.0, 4, prompt_ids=[5] * 20)])
     assert len(ok[0].token_ids) == 4
+
+
+def test_qwen3_0p6b_full_depth_logits():
+    """BASELINE config 0 architecture at full depth (28 layers, 151,936 vocabulary, tied head)."""
+    from byzantine_consensus_llm_agents_b200.model import PRESETS
+    cfg = PRESETS["qwen3-0.6b"]
+    hf = build_hf_model(cfg, seed=0)
+    w = Weights.from_hf_state_dict(cfg, hf.state_dict(), torch.device("cuda:0"))
+    tk = get_tokenizer(cfg.family, cfg.vocab)
+    eng = Engine(cfg, w, tk, max_model_len=2048, max_rows=4, prefill_tokens=2048, kv_pages=300)
+    rng = np.random.default_rng(5)
+    prompts = _prompts(tk, rng, [700, 130])
+    n_new = 6
+    forced = [rng.integers(*tk.regular_range, size=n_new).tolist() for _ in prompts]
+    eng.debug_logits = []
+    eng.generate([Request("", None, 0.0, n_new, forced=f, prompt_ids=p) for p, f in zip(prompts, forced)])
+    got = torch.stack(eng.debug_logits).cpu()
+    worst = 0.0
+    for b, (p, f) in enumerate(zip(prompts, forced)):
+        ref = full_logits(hf, p + f[:-1])[len(p) - 1:]
+        d = (got[:, b] - ref).abs()
+        worst = max(worst, d.max().item())
+        print(f"0.6B row {b}: max |dlogit| {d.max().item():.4f}  rms {d.pow(2).mean().sqrt().item():.5f} "
+              f"logit std {ref.std().item():.3f}")
+    assert worst <= LOGIT_TOL
