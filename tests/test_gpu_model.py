@@ -59,7 +59,8 @@ def test_logits_match_fp32_cpu_forward(cfg, tol):
         ref = ref[len(p) - 1:]                          # positions that predict the n_new tokens
         err = (got[:, b] - ref).abs().max().item()
         worst = max(worst, err)
-        assert err <= LOGIT_TOL, f"row {b} (prompt {len(p)}): max |dlogit| = {err}"
+        assert err <= tol, f"row {b} (prompt {len(p)}): max |dlogit| = {err}"
+        assert (got[:, b] - ref).pow(2).mean().sqrt().item() <= 6e-3
         assert res[b].token_ids == f
         # the sampler's own greedy pick agrees with the fp32 argmax wherever the fp32 top-1 margin
         # exceeds twice the logit tolerance
