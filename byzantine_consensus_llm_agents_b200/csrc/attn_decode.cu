@@ -13,6 +13,8 @@
 //
 // KV cache layout (one layer): [page][2 (k,v)][n_kv_heads][16 tokens][128] bf16 — a
 // (page, kv-head) K or V slab is 4 KB contiguous.
+#include <mutex>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -255,6 +257,82 @@ int decode_attn_paged(const void* q, const void* kv_cache, const int* block_tabl
       scratch_o, scratch_ml, seq_lens, reinterpret_cast<__nv_bfloat16*>(out), n_heads, max_splits);
   BCG_CUDA_CHECK(cudaGetLastError());
   return BCG_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// Allocation-free variant: bcg_decode_attn_paged_static
+//
+// bcg_decode_attn_paged needs two scratch buffers (the per-chunk partial outputs and their
+// softmax statistics) that the caller must allocate.  Some hosts cannot do that at the point
+// where they call attention: a serving process that handed its whole device-memory budget to
+// weights and KV pages at start-up has nothing left for a late cudaMalloc (and a failed
+// allocation in the middle of a game round would abort the round), and a latency-critical
+// decode loop must stay away from cudaMalloc / cudaFree because both synchronise the whole
+// device.  For those callers the scratch lives inside the library, in the fixed-size device
+// array below; the caller still passes q, the KV cache, the block table, seq_lens and out.
+//
+//   * Limit: B * n_heads * max_splits * 130 floats <= kStaticScratchFloats (4 Mi floats =
+//     16 MiB).  Larger problems are refused with BCG_STATUS_TOO_LARGE; use
+//     bcg_decode_attn_paged with caller-owned scratch instead.
+//   * Cost: every GPU that loads the library keeps these 16 MiB until the process exits.
+//   * The first call on each device looks the array's device address up
+//     (cudaGetSymbolAddress with that device current) and caches it; make that first call
+//     before any stream capture begins.  Later calls only launch kernels.
+//   * All calls on a device share the one array, and it keeps whatever the previous call left
+//     in it.  Nothing has to be cleared: phase 1 writes every (row, head, chunk) entry that
+//     phase 2 reads in the same call, and entries of chunks beyond a row's length are never
+//     read.  For the same reason two calls that overlap on the GPU (different streams) race on
+//     the array — issue them on one stream, or order them with events.
+// ---------------------------------------------------------------------------------------
+constexpr long long kStaticScratchFloats = 4ll * 1024 * 1024;
+constexpr int kMaxDevices = 64;
+
+// NOTE: in host code this name is only a host-side handle for the symbol, never a device
+// address; the device address is obtained once per device below.
+static __device__ __align__(256) float g_decode_scratch[kStaticScratchFloats];
+
+static std::mutex g_scratch_mu;
+static float* g_scratch_addr[kMaxDevices] = {};
+
+static int static_scratch_on_current_device(float** out) {
+  int dev = -1;
+  BCG_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) {
+    set_last_error("bcg_decode_attn_paged_static", "device ordinal out of range");
+    return BCG_ERR_UNSUPPORTED;
+  }
+  std::lock_guard<std::mutex> lock(g_scratch_mu);
+  if (!g_scratch_addr[dev]) {
+    void* p = nullptr;
+    BCG_CUDA_CHECK(cudaGetSymbolAddress(&p, g_decode_scratch));
+    g_scratch_addr[dev] = static_cast<float*>(p);
+  }
+  *out = g_scratch_addr[dev];
+  return BCG_OK;
+}
+
+int decode_attn_paged_static(const void* q, const void* kv_cache, const int* block_table,
+                             int max_blocks_per_seq, const int* seq_lens, void* out, int B,
+                             int n_heads, int n_kv_heads, int page_size, int max_splits, float scale,
+                             cudaStream_t stream) {
+  if (B <= 0 || n_heads <= 0 || max_splits <= 0) {
+    set_last_error("bcg_decode_attn_paged_static", "bad argument");
+    return BCG_ERR_ARG;
+  }
+  const long long n_o = static_cast<long long>(B) * n_heads * max_splits * 128;
+  const long long n_ml = static_cast<long long>(B) * n_heads * max_splits * 2;
+  if (n_o + n_ml > kStaticScratchFloats) {
+    set_last_error("bcg_decode_attn_paged_static",
+                   "B * n_heads * max_splits * 130 floats exceeds the built-in 16 MiB scratch; "
+                   "use bcg_decode_attn_paged with caller-owned scratch");
+    return BCG_ERR_TOO_LARGE;
+  }
+  float* scratch = nullptr;
+  const int rc = static_scratch_on_current_device(&scratch);
+  if (rc != BCG_OK) return rc;
+  return decode_attn_paged(q, kv_cache, block_table, max_blocks_per_seq, seq_lens, out, scratch,
+                           scratch + n_o, B, n_heads, n_kv_heads, page_size, max_splits, scale,
+                           stream);
 }
 
 }  // namespace bcg

@@ -77,6 +77,14 @@ int bcg_decode_attn_paged(const void* q, const void* kv_cache, const int* block_
                            S(stream));
 }
 
+int bcg_decode_attn_paged_static(const void* q, const void* kv_cache, const int* block_table,
+                                 int max_blocks_per_seq, const int* seq_lens, void* out, int B,
+                                 int n_heads, int n_kv_heads, int page_size, int max_splits,
+                                 float scale, void* stream) {
+  return decode_attn_paged_static(q, kv_cache, block_table, max_blocks_per_seq, seq_lens, out, B,
+                                  n_heads, n_kv_heads, page_size, max_splits, scale, S(stream));
+}
+
 int bcg_prefill_attn_paged(const void* q, const void* kv_cache, const int* block_table,
                            int max_blocks_per_seq, const int* tile_info, int n_tiles, void* out,
                            int n_heads, int n_kv_heads, int page_size, float scale, void* stream) {

@@ -77,6 +77,8 @@ _SIGS = {
     "bcg_swiglu_reduce": (C.c_int, [vp, C.c_int, C.c_longlong, vp, C.c_int, C.c_int, vp]),
     "bcg_decode_attn_paged": (C.c_int, [vp, vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, C.c_int,
                                         C.c_int, C.c_int, C.c_int, C.c_float, vp]),
+    "bcg_decode_attn_paged_static": (C.c_int, [vp, vp, vp, C.c_int, vp, vp, C.c_int, C.c_int, C.c_int,
+                                               C.c_int, C.c_int, C.c_float, vp]),
     "bcg_prefill_attn_paged": (C.c_int, [vp, vp, vp, C.c_int, vp, C.c_int, vp, C.c_int, C.c_int,
                                          C.c_int, C.c_float, vp]),
     "bcg_mask_sample": (C.c_int, [C.POINTER(SamplerArgs), vp]),

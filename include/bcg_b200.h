@@ -96,6 +96,21 @@ int bcg_decode_attn_paged(const void* q, const void* kv_cache, const int* block_
                           float* scratch_ml, int B, int n_heads, int n_kv_heads, int page_size,
                           int max_splits, float scale, void* stream);
 
+/* Same computation as bcg_decode_attn_paged, for callers that cannot allocate device memory.
+ * No counterpart in the reference (the reference never manages device memory itself); it exists
+ * for hosts of this library that have no memory left to give, or no safe moment to ask for it:
+ * a server whose whole device budget already went to weights and KV pages, or a decode loop that
+ * must avoid cudaMalloc/cudaFree because they synchronise the device.  The scratch is a 16 MiB
+ * array inside the library (held by every GPU that loads it, until exit), so the problem must
+ * satisfy B * n_heads * max_splits * 130 <= 4 * 1024 * 1024 floats; larger calls return
+ * BCG_STATUS_TOO_LARGE.  The first call on a device resolves the array's address — make it
+ * before any stream capture.  Calls share the array: keep them on one stream (overlapping calls
+ * race); nothing needs clearing between calls.  Allocates nothing, frees nothing. */
+int bcg_decode_attn_paged_static(const void* q, const void* kv_cache, const int* block_table,
+                                 int max_blocks_per_seq, const int* seq_lens, void* out, int B,
+                                 int n_heads, int n_kv_heads, int page_size, int max_splits,
+                                 float scale, void* stream);
+
 /* Causal attention of ragged new-token rows against cached prefix + new tokens, both read
  * through the block table.  tile_info: int32 [n_tiles][4] = {sequence, first q row, position
  * of that row in its sequence, rows (<= 64)}.
