@@ -14,8 +14,6 @@ What differs is underneath: `batch_generate_json` sends ALL rows to the engine i
 even when their schemas differ (the reference degrades to one prompt at a time,
 vllm_agent.py:449-455), and there is no `max_num_seqs` concurrency cap.
 """
-from __future__ import annotations
-
 import gc
 import io
 import json
@@ -189,8 +187,8 @@ class VLLMAgent:
         full = self._format_chat_prompt(system_prompt, prompt) if system_prompt else prompt
         return self.llm.run([full], [None], temperature, max_tokens)[0].strip()
 
-    def batch_generate(self, prompts: List[str], temperature: float = 0.0, max_tokens: int = 256,
-                       top_p: float = 1.0, **kwargs) -> List[str]:
+    def batch_generate(self, prompts: list[str], temperature: float = 0.0, max_tokens: int = 256,
+                       top_p: float = 1.0, **kwargs) -> list[str]:
         self._check_sampling(top_p, kwargs)
         if not prompts:
             return []
