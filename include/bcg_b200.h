@@ -164,7 +164,9 @@ typedef struct bcg_sampler_args {
   int* n_active;             /* [1] number of unfinished rows after this call, or NULL */
 } bcg_sampler_args;
 
-int bcg_mask_sample(const bcg_sampler_args* args /* host struct */, void* stream);
+/* Launches the sampler described above on `stream` (stands in for xgrammar's mask apply + vLLM's
+ * Sampler + accept_token bookkeeping).  `args` is a HOST struct of device pointers. */
+int bcg_mask_sample(const bcg_sampler_args* args, void* stream);
 
 /* Whole-model steps: the layer stack launched from C++ on one stream so a decode step is one
  * host call (captured into a CUDA graph by the engine).  See DESIGN.md §4. */
@@ -206,13 +208,15 @@ typedef struct bcg_workspace {
 } bcg_workspace;
 
 /* T new tokens (ragged over sequences) -> KV cache filled, logits of each sequence's last
- * token in ws->logits[0..n_seqs).  last_rows: device int32 [n_seqs]. */
+ * token in ws->logits[0..n_seqs).  last_rows: device int32 [n_seqs].  Stands in for one prefill
+ * pass of vLLM's Qwen3Model.forward + LogitsProcessor (models/qwen3.py:216-236, 328-333). */
 int bcg_model_prefill(const bcg_model* m, const bcg_workspace* ws, const int* ids,
                       const int* positions, const int* slot_map, const int* block_table,
                       int max_blocks_per_seq, const int* tile_info, int n_tiles,
                       const int* last_rows, int n_seqs, int T, void* stream);
 /* One decode step for B rows: ids/positions/slot_map/seq_lens are the arrays bcg_mask_sample
- * maintains; logits land in ws->logits[0..B). */
+ * maintains; logits land in ws->logits[0..B).  Stands in for one decode step of the same vLLM
+ * forward. */
 int bcg_model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids,
                      const int* positions, const int* slot_map, const int* seq_lens,
                      const int* block_table, int max_blocks_per_seq, int B, int flags,
