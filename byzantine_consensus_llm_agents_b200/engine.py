@@ -61,6 +61,7 @@ class Request:
     max_tokens: int = 256
     forced: Optional[Sequence[int]] = None     # teacher-forced ids (parity tests)
     prompt_ids: Optional[List[int]] = None     # pre-tokenised prompt (tests / bench)
+    seed: Optional[Sequence[int]] = None       # explicit Philox key (lo, hi); default: row_seed()
 
 
 @dataclass
@@ -369,7 +370,8 @@ class Engine:
         for b, pages in enumerate(pages_of):
             bt[b, :len(pages)] = pages
         gids = [self.grammar_index(q.schema) for q in reqs]
-        seeds = np.array([row_seed(self.base_seed, self.calls, row0 + b) for b in range(B)], np.uint32)
+        seeds = np.array([tuple(q.seed) if q.seed is not None else row_seed(self.base_seed, self.calls, row0 + b)
+                          for b, q in enumerate(reqs)], np.uint32)
         host_rows = dict(
             grammar_id=np.array(gids, np.int32), state=np.zeros(B, np.int32),
             temperature=np.array([q.temperature for q in reqs], np.float32),

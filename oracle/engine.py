@@ -68,12 +68,19 @@ class OracleEngine:
             if matcher is not None:
                 matcher.fill_next_token_bitmask(bm, 0)
                 mask = bm[0].numpy()
-            tok = S.sample(logits, mask, temperature, step, seed[0], seed[1])
-            if tok < 0:
+            # same arithmetic as S.sample(), kept open here so the decisive margin can be recorded:
+            # masked logits when greedy, masked race scores (logit/T - log q) when sampling
+            allowed = np.ones(logits.shape[0], bool) if mask is None else S.unpack_mask(mask, logits.shape[0])
+            if not allowed.any():
                 finish = "dead"
                 break
-            allowed = np.ones(logits.shape[0], bool) if mask is None else S.unpack_mask(mask, logits.shape[0])
-            ml = np.where(allowed, logits, -np.inf)
+            if temperature < 1e-5:
+                score = logits.astype(np.float32)
+            else:
+                score, _ = S.race_scores(logits, temperature, step, seed[0], seed[1])
+            ml = np.where(allowed, score, np.float32(-np.inf))
+            tok = int(np.argmax(ml))
+            assert tok == S.sample(logits, mask, temperature, step, seed[0], seed[1])
             part = np.partition(ml, -2)[-2:] if allowed.sum() > 1 else np.array([-np.inf, ml.max()])
             top1.append(float(part[1]))
             top2.append(float(part[0]))
@@ -95,7 +102,8 @@ class OracleEngine:
             logits = out.logits[0, -1].float().numpy()
         text = self.tk.decode([t for t in toks if t not in self.tk.stop_ids])
         return text, {"prompt_ids": len(ids), "tokens": toks, "top1": top1, "top2": top2,
-                      "finish": finish, "first_logits_max": float(first_logits.max())}
+                      "finish": finish, "first_logits_max": float(first_logits.max()),
+                      "seed": [int(seed[0]), int(seed[1])]}
 
     def __call__(self, prompts, sp):
         """vllm-shim backend: list of (text, extra)."""

@@ -58,16 +58,19 @@ def main():
     wall = time.time() - t0
     # de-duplicate identical (prompt, schema, max_tokens, temperature) generations
     uniq, calls = {}, []
-    for c in H.ShimLLM.calls:
+    for ci, c in enumerate(H.ShimLLM.calls):
         rows = []
-        for p, text, extra in zip(c.prompts, c.texts, c.extra):
-            key = json.dumps([p, c.schema, c.max_tokens, c.temperature])
+        for ri, (p, text, extra) in enumerate(zip(c.prompts, c.texts, c.extra)):
+            # greedy generations are a function of the request; sampled ones also of their seed
+            key = json.dumps([p, c.schema, c.max_tokens, c.temperature,
+                              None if c.temperature < 1e-5 else [ci, ri]])
             if key not in uniq:
                 uniq[key] = {"id": len(uniq), "prompt": p, "schema": c.schema, "max_tokens": c.max_tokens,
                              "temperature": c.temperature, "text": text, "tokens": extra["tokens"],
                              "top1": [round(x, 5) for x in extra["top1"]],
                              "top2": [round(x, 5) for x in extra["top2"]],
-                             "finish": extra["finish"], "prompt_tokens": extra["prompt_ids"]}
+                             "finish": extra["finish"], "prompt_tokens": extra["prompt_ids"],
+                             "seed": extra["seed"]}
             rows.append(uniq[key]["id"])
         calls.append({"rows": rows, "temperature": c.temperature, "max_tokens": c.max_tokens})
     keep = ["total_rounds", "consensus_reached", "final_consensus_value", "honest_agents_count",

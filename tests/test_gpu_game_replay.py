@@ -1,0 +1,103 @@
+"""Whole-game parity on the GPU, by replay (the reference itself cannot travel to the GPU box).
+
+tests/golden/game_*.json.gz hold complete seeded games of the UNMODIFIED reference played
+against the CPU oracle engine (transformers fp32 + xgrammar + oracle sampler), recorded at the
+`LLM.generate` boundary by oracle/tools/make_game_golden.py: every request (prompt, schema,
+temperature, max_tokens, seed) with its token stream, text and — per step — the two best
+decision scores (masked logits when greedy, masked race scores logit/T − log q when sampling).
+
+The game is a deterministic function of the engine's outputs, so an engine that reproduces every
+recorded output reproduces the transcript (proposed values, votes, termination round).  bf16
+kernels cannot match an fp32 forward bit for bit, so — as north_star allows — agreement is
+required exactly where the oracle's decision margin exceeds what a 2e-2 logit error can move:
+
+  1. teacher-forced pass: at every step whose margin is clear the engine's own pick must be the
+     recorded token (bit-exact grammar masks and RNG are implied: one wrong mask bit or random
+     draw would break it);
+  2. free-running pass: the engine's stream must equal the recorded one up to the first unclear
+     step, and entirely — text and finish reason included — when every step is clear.
+"""
+import glob
+import gzip
+import json
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from byzantine_consensus_llm_agents_b200.engine import Engine, Request  # noqa: E402
+from byzantine_consensus_llm_agents_b200.model import PRESETS, ModelConfig, Weights  # noqa: E402
+from byzantine_consensus_llm_agents_b200.tokenizer import get_tokenizer  # noqa: E402
+from oracle.model import build_hf_model  # noqa: E402
+
+LOGIT_TOL = 2e-2
+FIXTURES = sorted(glob.glob(str(Path(__file__).parent / "golden" / "game_*.json.gz")))
+
+
+def _clear(req, i):
+    """True if a logit error of LOGIT_TOL on both candidates cannot flip step i."""
+    margin = req["top1"][i] - req["top2"][i]
+    scale = 1.0 if req["temperature"] < 1e-5 else 1.0 / req["temperature"]
+    return margin > 2 * LOGIT_TOL * scale + 1e-4      # 1e-4: the fixture rounds scores to 5 decimals
+
+
+@pytest.mark.skipif(not FIXTURES, reason="no golden game fixtures")
+@pytest.mark.parametrize("path", FIXTURES, ids=lambda p: Path(p).name.replace(".json.gz", ""))
+def test_recorded_game_replays_on_the_engine(path):
+    with gzip.open(path, "rt") as f:
+        gold = json.load(f)
+    meta = gold["meta"]
+    cfg = PRESETS[meta["model"]]
+    if meta["layers"] != cfg.n_layers:
+        cfg = ModelConfig(**{**cfg.__dict__, "n_layers": meta["layers"], "name": f"{cfg.name}-L{meta['layers']}"})
+    hf = build_hf_model(cfg, seed=meta["weight_seed"])
+    w = Weights.from_hf_state_dict(cfg, hf.state_dict(), torch.device("cuda:0"))
+    del hf
+    tk = get_tokenizer(cfg.family, cfg.vocab)
+    eng = Engine(cfg, w, tk, max_model_len=8192, max_rows=16, prefill_tokens=16384, kv_pages=6000)
+    reqs = gold["requests"]
+
+    def run(forced: bool):
+        out = []
+        for i in range(0, len(reqs), 16):
+            wave = reqs[i:i + 16]
+            out.extend(eng.generate([
+                Request(r["prompt"], r["schema"], r["temperature"], r["max_tokens"],
+                        forced=r["tokens"] if forced else None, seed=r.get("seed")) for r in wave]))
+        return out
+
+    # ---- 1. teacher-forced
+    forced = run(True)
+    total = clear = wrong = 0
+    for r, g in zip(reqs, forced):
+        assert g.prompt_tokens == r["prompt_tokens"]                    # same tokenisation
+        assert g.token_ids == r["tokens"]
+        for i, (want, got) in enumerate(zip(r["tokens"], g.chosen)):
+            total += 1
+            if _clear(r, i):
+                clear += 1
+                wrong += (want != got)
+    assert wrong == 0, f"{wrong} of {clear} clear-margin steps disagree with the oracle"
+    assert clear / total > 0.5, "margins too thin for the fixture to test anything"
+
+    # ---- 2. free-running
+    eng.reset_prefix_cache()
+    free = run(False)
+    exact = 0
+    for r, g in zip(reqs, free):
+        n_clear_prefix = 0
+        while n_clear_prefix < len(r["tokens"]) and _clear(r, n_clear_prefix):
+            n_clear_prefix += 1
+        assert g.token_ids[:n_clear_prefix] == r["tokens"][:n_clear_prefix]
+        if n_clear_prefix == len(r["tokens"]):
+            exact += 1
+            assert g.token_ids == r["tokens"]
+            assert g.text == r["text"]
+            assert g.finish == {"stop": "stop", "length": "length", "dead": "dead"}[r["finish"]]
+    print(f"{Path(path).name}: {len(reqs)} generations, {total} steps, {100 * clear / total:.1f}% with a clear "
+          f"margin (all agree), {exact} generations reproduced end to end; transcript rounds: "
+          f"{len(gold['transcript'])}")
+    eng.close()
