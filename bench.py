@@ -261,6 +261,8 @@ def main():
     ap.add_argument("--honest", type=int, default=8)
     ap.add_argument("--byzantine", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--pdl", type=int, default=int(os.environ.get("BCG_B200_PDL", "1")),
+                    help="programmatic dependent launch for the decode step (1 = on)")
     a = ap.parse_args()
 
     rank = int(os.environ.get("RANK", 0))
@@ -272,7 +274,7 @@ def main():
     config = {"workload": f"{a.model} bf16 random-init, {a.honest} honest + {a.byzantine} Byzantine agents, "
                           "one game round per step (decide T=0.5/300 tok + vote T=0.3/200 tok, reference "
                           "retry schedule), recorded steady-state reference prompts",
-              "agents": n_agents, "rounds_recorded": len(rounds),
+              "agents": n_agents, "rounds_recorded": len(rounds), "pdl": bool(a.pdl),
               "parallelism": f"dp{world} (one independent game per GPU)" if world > 1 else "single GPU",
               "l2": "per-step inputs (27.98 GB of weights per decode step) exceed the 126 MB L2"}
 
@@ -308,7 +310,7 @@ def main():
     model_name = HF_NAME.get(a.model, a.model)
     model_config = {"max_model_len": 8192, "gpu_memory_utilization": 0.9, "tensor_parallel_size": 1,
                     "max_num_seqs": 4, "disable_qwen3_thinking": True, "device": f"cuda:{local_rank}",
-                    "seed": 1000 + rank, "engine_max_rows": max(16, n_agents)}
+                    "seed": 1000 + rank, "engine_max_rows": max(16, n_agents), "pdl": bool(a.pdl)}
     t_load = time.perf_counter()
     agent = VA.VLLMAgent("agent_0", model_name, model_config)
     engine = agent.llm.engine

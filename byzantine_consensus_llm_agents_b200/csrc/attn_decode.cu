@@ -46,6 +46,7 @@ decode_attn_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __r
   __shared__ float sm_acc[4][GH][128];
   __shared__ float sm_m[4][GH];
   __shared__ float sm_l[4][GH];
+  pdl_launch_dependents();
   pdl_wait();
   const int split = blockIdx.x;
   const int head0 = blockIdx.y * GH;
@@ -180,13 +181,13 @@ decode_attn_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __r
       }
     }
   }
-  pdl_launch_dependents();
 }
 
 __global__ void __launch_bounds__(128)
 decode_attn_merge_kernel(const float* __restrict__ scratch_o, const float* __restrict__ scratch_ml,
                          const int* __restrict__ seq_lens, __nv_bfloat16* __restrict__ out,
                          int n_heads, int max_splits) {
+  pdl_launch_dependents();
   pdl_wait();
   const int head = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
   const int seq_len = seq_lens[b];
@@ -203,7 +204,6 @@ decode_attn_merge_kernel(const float* __restrict__ scratch_o, const float* __res
   }
   const float r = ll > 0.f ? o / ll : 0.f;
   out[(static_cast<long long>(b) * n_heads + head) * 128 + tid] = __float2bfloat16_rn(r);
-  pdl_launch_dependents();
 }
 
 template <int G, int GH>
@@ -212,11 +212,11 @@ static int launch_decode(const void* q, const void* kv_cache, const int* block_t
                          int B, int n_heads, int n_kv_heads, int max_splits, float scale,
                          cudaStream_t stream) {
   dim3 grid(max_splits, n_heads / GH, B);
-  decode_attn_kernel<G, GH><<<grid, 128, 0, stream>>>(
-      reinterpret_cast<const __nv_bfloat16*>(q), reinterpret_cast<const __nv_bfloat16*>(kv_cache),
-      block_table, max_blocks, seq_lens, scratch_o, scratch_ml, n_heads, n_kv_heads, max_splits,
-      scale * 1.4426950408889634f);
-  BCG_CUDA_CHECK(cudaGetLastError());
+  BCG_CUDA_CHECK(launch_k(decode_attn_kernel<G, GH>, grid, dim3(128), 0, stream,
+                          reinterpret_cast<const __nv_bfloat16*>(q),
+                          reinterpret_cast<const __nv_bfloat16*>(kv_cache), block_table, max_blocks,
+                          seq_lens, scratch_o, scratch_ml, n_heads, n_kv_heads, max_splits,
+                          scale * 1.4426950408889634f));
   return BCG_OK;
 }
 
@@ -253,9 +253,9 @@ int decode_attn_paged(const void* q, const void* kv_cache, const int* block_tabl
   }
 #undef BCG_DECODE_CASE
   if (rc != BCG_OK) return rc;
-  decode_attn_merge_kernel<<<dim3(n_heads, B), 128, 0, stream>>>(
-      scratch_o, scratch_ml, seq_lens, reinterpret_cast<__nv_bfloat16*>(out), n_heads, max_splits);
-  BCG_CUDA_CHECK(cudaGetLastError());
+  BCG_CUDA_CHECK(launch_k(decode_attn_merge_kernel, dim3(n_heads, B), dim3(128), 0, stream,
+                          static_cast<const float*>(scratch_o), static_cast<const float*>(scratch_ml),
+                          seq_lens, reinterpret_cast<__nv_bfloat16*>(out), n_heads, max_splits));
   return BCG_OK;
 }
 

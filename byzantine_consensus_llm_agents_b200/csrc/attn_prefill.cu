@@ -57,6 +57,7 @@ prefill_attn_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __
   uint8_t* sQ = pf_smem;                       // 16 KB
   uint8_t* sK = pf_smem + 16384;               // 2 x 16 KB
   uint8_t* sV = pf_smem + 16384 + 2 * 16384;   // 2 x 16 KB
+  pdl_launch_dependents();
   pdl_wait();
 
   const int tile = blockIdx.x, head = blockIdx.y;
@@ -199,7 +200,6 @@ prefill_attn_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __
       }
     }
   }
-  pdl_launch_dependents();
 }
 
 int prefill_attn_paged(const void* q, const void* kv_cache, const int* block_table,

@@ -10,6 +10,11 @@ namespace bcg {
 
 static thread_local std::string g_last_error;
 
+int& launch_flags() {
+  static thread_local int flags = 0;
+  return flags;
+}
+
 void set_last_error(const char* what, const char* detail) {
   g_last_error = std::string(what ? what : "?") + ": " + (detail ? detail : "");
 }

@@ -30,6 +30,29 @@ enum : int {
 
 void set_last_error(const char* what, const char* detail);
 
+// Launch flags of the calling thread's current composite step (set by model_decode): when
+// BCG_GEMM_PDL is on, every kernel of the step is launched with programmatic stream
+// serialisation, i.e. it may start while its predecessor is still running; each kernel
+// announces its dependents at entry (griddepcontrol.launch_dependents) and waits for its
+// predecessor's results with griddepcontrol.wait before touching them.
+int& launch_flags();
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                            cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = (launch_flags() & 1) ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // ----------------------------------------------------------------------------
 // shared-memory address / mbarrier
 // ----------------------------------------------------------------------------

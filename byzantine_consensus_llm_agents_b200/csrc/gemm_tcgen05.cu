@@ -68,6 +68,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  pdl_launch_dependents();
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -301,7 +302,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
   }
 
-  pdl_launch_dependents();
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
@@ -388,18 +388,31 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmA
   return BCG_OK;
 }
 
+// Split-K factor for the decode path.  Depends on (N, K) only — never on the number of rows — so
+// a row's arithmetic is the same whatever batch it is in.  Work items = tiles x splits are dealt
+// round-robin to 148 persistent CTAs; the factor is chosen to fill whole waves (e.g. 40 tiles x 7
+// = 280 items = 1.89 waves -> 94.6 % instead of 40 x 8 = 320 = 2.16 waves -> 72 %), discounted by
+// the fp32 partial traffic it adds (4*s*16/K of the weight bytes at 16 rows).
 int gemm_splits_for(int M, int N, int K) {
   if (M > 128) return 1;
   const int tiles = (N + kBlockA - 1) / kBlockA;
   const int kb = (K + kBlockK - 1) / kBlockK;
   const int sms = 148;
-  if (tiles >= sms) return 1;
-  int s = (2 * sms + tiles - 1) / tiles;  // aim for ~2 work items per SM
-  const int max_s = kb / 4 > 0 ? kb / 4 : 1;  // keep >= 4 k-blocks (32 KB of weights) per item
-  if (s > max_s) s = max_s;
-  if (s > 16) s = 16;
-  if (s < 1) s = 1;
-  return s;
+  int best = 1;
+  double best_score = -1.0;
+  for (int s = 1; s <= 16; ++s) {
+    if (s > 1 && kb / s < 4) break;  // keep >= 4 k-blocks (32 KB of weights) per item
+    const int items = tiles * s;
+    const int rounds = (items + sms - 1) / sms;
+    const double eff = static_cast<double>(items) / (static_cast<double>(rounds) * sms);
+    const double extra = (s > 1) ? 4.0 * s * 16.0 / K : 0.0;
+    const double score = eff / (1.0 + extra);
+    if (score > best_score + 0.02) {  // need a real gain to split further
+      best_score = score;
+      best = s;
+    }
+  }
+  return best;
 }
 
 int gemm_bf16_tn(const void* X, const void* W, void* out, int M, int N, int K, long long ldx,
@@ -439,7 +452,7 @@ int gemm_bf16_tn(const void* X, const void* W, void* out, int M, int N, int K, l
   a.epi = epi;
   a.out = out;
   a.ld_out = ld_out;
-  a.pdl_wait_b = (flags & BCG_GEMM_PDL) ? 1 : 0;
+  a.pdl_wait_b = ((flags | launch_flags()) & BCG_GEMM_PDL) ? 1 : 0;
   int bn;
   if (swap) {
     bn = M <= 16 ? 16 : M <= 32 ? 32 : M <= 64 ? 64 : 128;

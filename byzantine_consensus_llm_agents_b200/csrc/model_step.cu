@@ -95,6 +95,11 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
     return BCG_ERR_TOO_LARGE;
   }
   const int gf = flags & BCG_GEMM_PDL;
+  struct FlagScope {
+    int saved;
+    explicit FlagScope(int f) : saved(launch_flags()) { launch_flags() = f; }
+    ~FlagScope() { launch_flags() = saved; }
+  } scope(gf);
   float* P = ws->partials;
   for (int l = 0; l < m->n_layers; ++l) {
     if (l == 0) {

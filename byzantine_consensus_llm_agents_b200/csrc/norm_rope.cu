@@ -14,16 +14,17 @@
 
 namespace bcg {
 
-constexpr int kNormThreads = 256;
-constexpr int kMaxVecPerThread = 8;  // d <= 256 * 8 * 4 = 8192
+constexpr int kNormThreads = 1024;
+constexpr int kMaxVecPerThread = 2;  // d <= 1024 * 2 * 4 = 8192
+constexpr int kMaxPartialsBatch = 8;
 
-__device__ __forceinline__ float block_sum_256(float v, float* red) {
+__device__ __forceinline__ float block_sum(float v, float* red) {
   v = warp_sum(v);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (lane == 0) red[warp] = v;
   __syncthreads();
   float t = 0.f;
-  // fixed order over the 8 warps: deterministic
+  // fixed order over the warps: deterministic
 #pragma unroll
   for (int i = 0; i < kNormThreads / 32; ++i) t += red[i];
   __syncthreads();
@@ -42,6 +43,7 @@ embed_rmsnorm_kernel(const int* __restrict__ ids, const __nv_bfloat16* __restric
                      const float* __restrict__ w, float* __restrict__ residual,
                      __nv_bfloat16* __restrict__ xn, int d, float eps) {
   __shared__ float red[kNormThreads / 32];
+  pdl_launch_dependents();
   pdl_wait();
   const int t = blockIdx.x;
   const long long row = ids[t];
@@ -57,7 +59,7 @@ embed_rmsnorm_kernel(const int* __restrict__ ids, const __nv_bfloat16* __restric
       ss += x[i].x * x[i].x + x[i].y * x[i].y + x[i].z * x[i].z + x[i].w * x[i].w;
     }
   }
-  const float tot = block_sum_256(ss, red);
+  const float tot = block_sum(ss, red);
   const float inv = rsqrtf(tot / static_cast<float>(d) + eps);
 #pragma unroll
   for (int i = 0; i < kMaxVecPerThread; ++i) {
@@ -69,7 +71,6 @@ embed_rmsnorm_kernel(const int* __restrict__ ids, const __nv_bfloat16* __restric
                    x[i].y * inv * ww.y, x[i].z * inv * ww.z, x[i].w * inv * ww.w);
     }
   }
-  pdl_launch_dependents();
 }
 
 // src_rows == nullptr: in-place residual update over all T rows.
@@ -81,6 +82,7 @@ add_rmsnorm_kernel(float* __restrict__ residual, const void* __restrict__ delta,
                    __nv_bfloat16* __restrict__ xn, const int* __restrict__ src_rows, int d,
                    float eps) {
   __shared__ float red[kNormThreads / 32];
+  pdl_launch_dependents();
   pdl_wait();
   const int t = blockIdx.x;
   const long long src = src_rows ? src_rows[t] : t;
@@ -95,10 +97,25 @@ add_rmsnorm_kernel(float* __restrict__ residual, const void* __restrict__ delta,
       if (delta) {
         if (delta_is_f32) {
           const float* dp = reinterpret_cast<const float*>(delta) + src * d + v * 4;
-          float4 acc = *reinterpret_cast<const float4*>(dp);
-          for (int s = 1; s < n_partials; ++s) {
-            const float4 p = *reinterpret_cast<const float4*>(dp + s * partial_stride);
-            acc.x += p.x; acc.y += p.y; acc.z += p.z; acc.w += p.w;
+          // issue all partial loads first (independent, up to 8 in flight), then add them in
+          // index order: same arithmetic as a serial loop, a fraction of its latency
+          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int s0 = 0; s0 < n_partials; s0 += kMaxPartialsBatch) {
+            float4 p[kMaxPartialsBatch];
+#pragma unroll
+            for (int s = 0; s < kMaxPartialsBatch; ++s) {
+              if (s0 + s < n_partials) p[s] = *reinterpret_cast<const float4*>(dp + (s0 + s) * partial_stride);
+            }
+#pragma unroll
+            for (int s = 0; s < kMaxPartialsBatch; ++s) {
+              if (s0 + s < n_partials) {
+                if (s0 + s == 0) {
+                  acc = p[s];
+                } else {
+                  acc.x += p[s].x; acc.y += p[s].y; acc.z += p[s].z; acc.w += p[s].w;
+                }
+              }
+            }
           }
           r.x += acc.x; r.y += acc.y; r.z += acc.z; r.w += acc.w;
         } else {
@@ -111,7 +128,7 @@ add_rmsnorm_kernel(float* __restrict__ residual, const void* __restrict__ delta,
       ss += r.x * r.x + r.y * r.y + r.z * r.z + r.w * r.w;
     }
   }
-  const float tot = block_sum_256(ss, red);
+  const float tot = block_sum(ss, red);
   const float inv = rsqrtf(tot / static_cast<float>(d) + eps);
 #pragma unroll
   for (int i = 0; i < kMaxVecPerThread; ++i) {
@@ -123,7 +140,6 @@ add_rmsnorm_kernel(float* __restrict__ residual, const void* __restrict__ delta,
                    x[i].y * inv * ww.y, x[i].z * inv * ww.z, x[i].w * inv * ww.w);
     }
   }
-  pdl_launch_dependents();
 }
 
 // One warp per (token, head).  head_dim is fixed at 128: lane l owns dims {2l, 2l+1} and
@@ -137,6 +153,7 @@ qknorm_rope_kvwrite_kernel(const void* __restrict__ qkv, int qkv_is_f32, int n_p
                            const int* __restrict__ slot_map, __nv_bfloat16* __restrict__ q_out,
                            __nv_bfloat16* __restrict__ kv_cache, int T, int n_heads, int n_kv_heads,
                            int page_size, float eps) {
+  pdl_launch_dependents();
   pdl_wait();
   const int lane = threadIdx.x & 31;
   const int heads_total = n_heads + 2 * n_kv_heads;
@@ -200,13 +217,13 @@ qknorm_rope_kvwrite_kernel(const void* __restrict__ qkv, int qkv_is_f32, int n_p
       }
     }
   }
-  pdl_launch_dependents();
 }
 
 // act[t, f] = silu(gate) * up where the GEMM's N axis is interleaved [16 gate | 16 up].
 __global__ void __launch_bounds__(256)
 swiglu_reduce_kernel(const float* __restrict__ partials, int n_partials, long long partial_stride,
                      __nv_bfloat16* __restrict__ act, long long total_out, int f) {
+  pdl_launch_dependents();
   pdl_wait();
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i < total_out) {
@@ -221,7 +238,6 @@ swiglu_reduce_kernel(const float* __restrict__ partials, int n_partials, long lo
     }
     act[i] = __float2bfloat16_rn(g * (1.0f / (1.0f + __expf(-g))) * u);
   }
-  pdl_launch_dependents();
 }
 
 // ---------------------------------------------------------------------------------------
@@ -233,10 +249,9 @@ int embed_rmsnorm(const int* ids, const void* embed, const float* w, float* resi
     set_last_error("bcg_embed_rmsnorm", "bad argument (d must be a multiple of 4 and <= 8192)");
     return BCG_ERR_ARG;
   }
-  embed_rmsnorm_kernel<<<T, kNormThreads, 0, stream>>>(
-      ids, reinterpret_cast<const __nv_bfloat16*>(embed), w, residual,
-      reinterpret_cast<__nv_bfloat16*>(xn), d, eps);
-  BCG_CUDA_CHECK(cudaGetLastError());
+  BCG_CUDA_CHECK(launch_k(embed_rmsnorm_kernel, dim3(T), dim3(kNormThreads), 0, stream, ids,
+                          reinterpret_cast<const __nv_bfloat16*>(embed), w, residual,
+                          reinterpret_cast<__nv_bfloat16*>(xn), d, eps));
   return BCG_OK;
 }
 
@@ -248,11 +263,9 @@ int add_rmsnorm(float* residual, const void* delta, int delta_is_f32, int n_part
     set_last_error("bcg_add_rmsnorm", "bad argument (d must be a multiple of 4 and <= 8192)");
     return BCG_ERR_ARG;
   }
-  add_rmsnorm_kernel<<<T, kNormThreads, 0, stream>>>(residual, delta, delta_is_f32, n_partials,
-                                                     partial_stride, w,
-                                                     reinterpret_cast<__nv_bfloat16*>(xn), src_rows,
-                                                     d, eps);
-  BCG_CUDA_CHECK(cudaGetLastError());
+  BCG_CUDA_CHECK(launch_k(add_rmsnorm_kernel, dim3(T), dim3(kNormThreads), 0, stream, residual, delta,
+                          delta_is_f32, n_partials, partial_stride, w,
+                          reinterpret_cast<__nv_bfloat16*>(xn), src_rows, d, eps));
   return BCG_OK;
 }
 
@@ -268,11 +281,11 @@ int qknorm_rope_kvwrite(const void* qkv, int qkv_is_f32, int n_partials, long lo
   }
   const long long warps = static_cast<long long>(T) * (n_heads + 2 * n_kv_heads);
   const unsigned grid = static_cast<unsigned>((warps + 3) / 4);
-  qknorm_rope_kvwrite_kernel<<<grid, 128, 0, stream>>>(
-      qkv, qkv_is_f32, n_partials, partial_stride, ld_qkv, q_norm_w, k_norm_w, cos_sin, positions,
-      slot_map, reinterpret_cast<__nv_bfloat16*>(q_out), reinterpret_cast<__nv_bfloat16*>(kv_cache),
-      T, n_heads, n_kv_heads, page_size, eps);
-  BCG_CUDA_CHECK(cudaGetLastError());
+  BCG_CUDA_CHECK(launch_k(qknorm_rope_kvwrite_kernel, dim3(grid), dim3(128), 0, stream, qkv, qkv_is_f32,
+                          n_partials, partial_stride, ld_qkv, q_norm_w, k_norm_w, cos_sin, positions,
+                          slot_map, reinterpret_cast<__nv_bfloat16*>(q_out),
+                          reinterpret_cast<__nv_bfloat16*>(kv_cache), T, n_heads, n_kv_heads, page_size,
+                          eps));
   return BCG_OK;
 }
 
@@ -284,9 +297,9 @@ int swiglu_reduce(const float* partials, int n_partials, long long partial_strid
   }
   const int f = two_f / 2;
   const long long total = static_cast<long long>(T) * f;
-  swiglu_reduce_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(
-      partials, n_partials, partial_stride, reinterpret_cast<__nv_bfloat16*>(act), total, f);
-  BCG_CUDA_CHECK(cudaGetLastError());
+  BCG_CUDA_CHECK(launch_k(swiglu_reduce_kernel, dim3(static_cast<unsigned>((total + 255) / 256)),
+                          dim3(256), 0, stream, partials, n_partials, partial_stride,
+                          reinterpret_cast<__nv_bfloat16*>(act), total, f));
   return BCG_OK;
 }
 

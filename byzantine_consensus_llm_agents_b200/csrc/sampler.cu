@@ -87,6 +87,7 @@ mask_sample_kernel(const SamplerDev p) {
   cg::cluster_group cluster = cg::this_cluster();
   __shared__ Best warp_best[kSampThreads / 32];
   __shared__ Best cta_best[kSampCluster];  // only CTA 0's copy is used
+  pdl_launch_dependents();
   pdl_wait();
 
   const int row = blockIdx.y;
@@ -195,11 +196,12 @@ mask_sample_kernel(const SamplerDev p) {
       a.slot_map[row] = -1;
     }
   }
-  pdl_launch_dependents();
 }
 
 // n_active[0] = number of rows still running (one small block; lets the host poll one int).
 __global__ void count_active_kernel(const int* __restrict__ finished, int B, int* n_active) {
+  pdl_launch_dependents();
+  pdl_wait();
   int c = 0;
   for (int i = threadIdx.x; i < B; i += 32) c += (finished[i] == 0);
 #pragma unroll
@@ -218,11 +220,10 @@ int mask_sample(const bcg_sampler_args* a, cudaStream_t stream) {
   }
   SamplerDev p;
   p.a = *a;
-  mask_sample_kernel<<<dim3(kSampCluster, a->B), kSampThreads, 0, stream>>>(p);
-  BCG_CUDA_CHECK(cudaGetLastError());
+  BCG_CUDA_CHECK(launch_k(mask_sample_kernel, dim3(kSampCluster, a->B), dim3(kSampThreads), 0, stream, p));
   if (a->n_active) {
-    count_active_kernel<<<1, 32, 0, stream>>>(a->finished, a->B, a->n_active);
-    BCG_CUDA_CHECK(cudaGetLastError());
+    BCG_CUDA_CHECK(launch_k(count_active_kernel, dim3(1), dim3(32), 0, stream,
+                            static_cast<const int*>(a->finished), a->B, a->n_active));
   }
   return BCG_OK;
 }
