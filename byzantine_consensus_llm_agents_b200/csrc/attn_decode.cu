@@ -4,10 +4,10 @@
 // row's arithmetic — chunk boundaries and the order partial results are merged in —
 // depends only on that row's own length, never on which other rows share the batch.
 //
-// Phase 1  decode_attn_kernel  grid (max_splits, n_heads / GH, B), 128 threads:
-//          each warp streams whole pages with 128-bit non-allocating loads (two tokens per
-//          load instruction, 16 loads in flight per lane), online softmax in fp32 with
-//          half-warp shuffle reductions, partial (m, l, o[128]) per (row, head, chunk) to
+// Phase 1  decode_attn_kernel  grid (max_splits, n_kv_heads, B), 128 threads:
+//          each warp streams whole pages with 128-bit non-allocating loads straight into
+//          tensor-core fragments (16 loads in flight per lane), QK^T and PV on m16n8k16 bf16
+//          MMAs, online softmax in fp32, partial (m, l, o[128]) per (row, head, chunk) to
 //          scratch.
 // Phase 2  decode_attn_merge_kernel  grid (n_heads, B): fixed-order merge of the chunks.
 //
@@ -23,158 +23,169 @@ namespace bcg {
 constexpr int kSplitTokens = 256;
 constexpr int kPage = 16;
 
-__device__ __forceinline__ float dot8(const float* q, const uint4& k) {
-  float s = q[0] * bf16lo(k.x);
-  s = fmaf(q[1], bf16hi(k.x), s);
-  s = fmaf(q[2], bf16lo(k.y), s);
-  s = fmaf(q[3], bf16hi(k.y), s);
-  s = fmaf(q[4], bf16lo(k.z), s);
-  s = fmaf(q[5], bf16hi(k.z), s);
-  s = fmaf(q[6], bf16lo(k.w), s);
-  s = fmaf(q[7], bf16hi(k.w), s);
-  return s;
+__device__ __forceinline__ void mma_bf16_16816(float* c, uint32_t a0, uint32_t a1, uint32_t a2,
+                                               uint32_t a3, uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, "
+      "{%8, %9}, {%0, %1, %2, %3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
-// G = q-heads per KV head, GH = q-heads handled by one CTA (GH divides G).
-template <int G, int GH>
+// G = q-heads per KV head (1..8).  One CTA = one (row, KV head, 256-token chunk); each of the 4
+// warps walks whole pages.  Both products run on bf16 tensor-core MMAs (m16n8k16, fp32
+// accumulate) with the G query heads as MMA rows 0..G-1 (rows G..15 are zero padding — the
+// kernel is HBM-bound, the spare tensor rows cost nothing).  No shared-memory staging: a dot
+// product does not care in which order its terms are added, so the MMA k-index is PERMUTED to
+// match what a 128-bit global load delivers —
+//   S = Q K^T : lane (g,t) loads 4 x 16 B of token g's K row (dims 8(t+4j)..+7, j=0..3: the four
+//               lanes of a quad cover 64 contiguous bytes per load instruction) and feeds them as
+//               the B fragments of the 8 k-steps; Q's A fragments use the same dim order.
+//   O = P V   : lane (g,t) loads 2 x 16 B (dims 16g..16g+15) of V rows 2t, 2t+1, 8+2t, 9+2t —
+//               exactly the tokens whose probabilities it holds in its S accumulators — and
+//               interleaves them pairwise (PRMT) into B fragments; output column g of MMA n-tile
+//               j is head dim 16g + j.
+template <int G>
 __global__ void __launch_bounds__(128)
 decode_attn_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ kv_cache,
                    const int* __restrict__ block_table, int max_blocks,
                    const int* __restrict__ seq_lens, float* __restrict__ scratch_o,
                    float* __restrict__ scratch_ml, int n_heads, int n_kv_heads, int max_splits,
                    float scale_log2e) {
-  __shared__ float sm_acc[4][GH][128];
-  __shared__ float sm_m[4][GH];
-  __shared__ float sm_l[4][GH];
+  __shared__ float sm_acc[4][G][128];
+  __shared__ float sm_m[4][G];
+  __shared__ float sm_l[4][G];
   pdl_launch_dependents();
   pdl_wait();
   const int split = blockIdx.x;
-  const int head0 = blockIdx.y * GH;
-  const int kvh = head0 / G;
+  const int kvh = blockIdx.y;
+  const int head0 = kvh * G;
   const int b = blockIdx.z;
   const int seq_len = seq_lens[b];
   const int n_splits = (seq_len + kSplitTokens - 1) / kSplitTokens;
   if (split < n_splits) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int half = lane >> 4, dl = lane & 15;
+    const int g = lane >> 2, t = lane & 3;
     const int tok0 = split * kSplitTokens;
     const int tok1 = min(seq_len, tok0 + kSplitTokens);
 
-    float qv[GH][8];
+    // Q as A fragments: [k-step][a0 (k 2t,2t+1), a2 (k 8+2t,9+2t)]; rows 8..15 (a1, a3) are zero
+    uint32_t qa[8][2];
 #pragma unroll
-    for (int g = 0; g < GH; ++g) {
-      const uint4 raw = *reinterpret_cast<const uint4*>(
-          q + (static_cast<long long>(b) * n_heads + head0 + g) * 128 + 8 * dl);
-      qv[g][0] = bf16lo(raw.x) * scale_log2e; qv[g][1] = bf16hi(raw.x) * scale_log2e;
-      qv[g][2] = bf16lo(raw.y) * scale_log2e; qv[g][3] = bf16hi(raw.y) * scale_log2e;
-      qv[g][4] = bf16lo(raw.z) * scale_log2e; qv[g][5] = bf16hi(raw.z) * scale_log2e;
-      qv[g][6] = bf16lo(raw.w) * scale_log2e; qv[g][7] = bf16hi(raw.w) * scale_log2e;
+    for (int j = 0; j < 4; ++j) {
+      uint4 raw = make_uint4(0u, 0u, 0u, 0u);
+      if (g < G) {
+        raw = *reinterpret_cast<const uint4*>(q + (static_cast<long long>(b) * n_heads + head0 + g) * 128 +
+                                              8 * (t + 4 * j));
+      }
+      qa[2 * j][0] = raw.x; qa[2 * j][1] = raw.y;
+      qa[2 * j + 1][0] = raw.z; qa[2 * j + 1][1] = raw.w;
     }
-    float m[GH], l[GH], acc[GH][8];
+    float o[16][4];
 #pragma unroll
-    for (int g = 0; g < GH; ++g) {
-      m[g] = -INFINITY;
-      l[g] = 0.f;
-#pragma unroll
-      for (int i = 0; i < 8; ++i) acc[g][i] = 0.f;
-    }
+    for (int j = 0; j < 16; ++j) o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f;
+    float m_run = -INFINITY, l_run = 0.f;  // row g (replicated over the quad; l is a quad-partial)
 
     for (int pg = tok0 / kPage + warp; pg * kPage < tok1; pg += 4) {
       const int phys = block_table[static_cast<long long>(b) * max_blocks + pg];
       const __nv_bfloat16* kbase =
           kv_cache + ((static_cast<long long>(phys) * 2 * n_kv_heads) + kvh) * (kPage * 128);
       const __nv_bfloat16* vbase = kbase + static_cast<long long>(n_kv_heads) * (kPage * 128);
-      uint4 kr[8], vr[8];
+      uint4 kf[2][4], vf[4][2];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) kr[j] = ldg_nc_v4(kbase + (2 * j + half) * 128 + 8 * dl);
+      for (int nt = 0; nt < 2; ++nt)
 #pragma unroll
-      for (int j = 0; j < 8; ++j) vr[j] = ldg_nc_v4(vbase + (2 * j + half) * 128 + 8 * dl);
-
-      float s[8][GH];
+        for (int j = 0; j < 4; ++j) kf[nt][j] = ldg_nc_v4(kbase + (nt * 8 + g) * 128 + 8 * (t + 4 * j));
+      const int vt[4] = {2 * t, 2 * t + 1, 8 + 2 * t, 9 + 2 * t};
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const bool valid = pg * kPage + 2 * j + half < tok1;
+      for (int i = 0; i < 4; ++i) {
+        vf[i][0] = ldg_nc_v4(vbase + vt[i] * 128 + 16 * g);
+        vf[i][1] = ldg_nc_v4(vbase + vt[i] * 128 + 16 * g + 8);
+      }
+      // ---- S = Q K^T
+      float s[2][4];
 #pragma unroll
-        for (int g = 0; g < GH; ++g) {
-          float d = dot8(qv[g], kr[j]);
-          d += __shfl_xor_sync(0xffffffffu, d, 8);
-          d += __shfl_xor_sync(0xffffffffu, d, 4);
-          d += __shfl_xor_sync(0xffffffffu, d, 2);
-          d += __shfl_xor_sync(0xffffffffu, d, 1);
-          s[j][g] = valid ? d : -INFINITY;
+      for (int nt = 0; nt < 2; ++nt) {
+        s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          mma_bf16_16816(s[nt], qa[2 * j][0], 0u, qa[2 * j][1], 0u, kf[nt][j].x, kf[nt][j].y);
+          mma_bf16_16816(s[nt], qa[2 * j + 1][0], 0u, qa[2 * j + 1][1], 0u, kf[nt][j].z, kf[nt][j].w);
         }
       }
+      // ---- online softmax of row g over this page's 16 tokens (this lane: tokens vt[0..3])
+      const int base_tok = pg * kPage;
+      float sv[4];
+      bool ok[4];
 #pragma unroll
-      for (int g = 0; g < GH; ++g) {
-        float mx = s[0][g];
+      for (int i = 0; i < 4; ++i) {
+        ok[i] = base_tok + vt[i] < tok1;
+        sv[i] = ok[i] ? s[i >> 1][i & 1] * scale_log2e : -INFINITY;
+      }
+      float mx = fmaxf(fmaxf(sv[0], sv[1]), fmaxf(sv[2], sv[3]));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+      const float m_new = fmaxf(m_run, mx);
+      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+      const float corr = exp2f(m_run - m_use);
+      m_run = m_new;
+      float p[4];
 #pragma unroll
-        for (int j = 1; j < 8; ++j) mx = fmaxf(mx, s[j][g]);
-        const float m_new = fmaxf(m[g], mx);
-        const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
-        const float corr = exp2f(m[g] - m_use);  // m == -inf -> 0
-        l[g] *= corr;
+      for (int i = 0; i < 4; ++i) p[i] = exp2f(sv[i] - m_use);
+      l_run = l_run * corr + (p[0] + p[1]) + (p[2] + p[3]);
+      const uint32_t pa0 = pack_bf16(p[0], p[1]);
+      const uint32_t pa2 = pack_bf16(p[2], p[3]);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) acc[g][i] *= corr;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float p = exp2f(s[j][g] - m_use);  // invalid -> 0
-          l[g] += p;
-          acc[g][0] = fmaf(p, bf16lo(vr[j].x), acc[g][0]);
-          acc[g][1] = fmaf(p, bf16hi(vr[j].x), acc[g][1]);
-          acc[g][2] = fmaf(p, bf16lo(vr[j].y), acc[g][2]);
-          acc[g][3] = fmaf(p, bf16hi(vr[j].y), acc[g][3]);
-          acc[g][4] = fmaf(p, bf16lo(vr[j].z), acc[g][4]);
-          acc[g][5] = fmaf(p, bf16hi(vr[j].z), acc[g][5]);
-          acc[g][6] = fmaf(p, bf16lo(vr[j].w), acc[g][6]);
-          acc[g][7] = fmaf(p, bf16hi(vr[j].w), acc[g][7]);
+      for (int i = 0; i < 4; ++i) {
+        if (!ok[i]) {  // never multiply stale cache contents (possibly non-finite) by p = 0
+          vf[i][0] = make_uint4(0u, 0u, 0u, 0u);
+          vf[i][1] = make_uint4(0u, 0u, 0u, 0u);
         }
-        m[g] = m_new;
+      }
+      // ---- O = O * corr + P V
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        o[j][0] *= corr;
+        o[j][1] *= corr;
+        const int h = j >> 3, w = (j & 7) >> 1;
+        const uint32_t sel = (j & 1) ? 0x7632u : 0x5410u;
+        const uint32_t* v0 = reinterpret_cast<const uint32_t*>(&vf[0][h]);
+        const uint32_t* v1 = reinterpret_cast<const uint32_t*>(&vf[1][h]);
+        const uint32_t* v2 = reinterpret_cast<const uint32_t*>(&vf[2][h]);
+        const uint32_t* v3 = reinterpret_cast<const uint32_t*>(&vf[3][h]);
+        const uint32_t b0 = __byte_perm(v0[w], v1[w], sel);
+        const uint32_t b1 = __byte_perm(v2[w], v3[w], sel);
+        mma_bf16_16816(o[j], pa0, 0u, pa2, 0u, b0, b1);
       }
     }
-
-    // merge the two half-warps (disjoint token sets), then the four warps via smem
+    l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
+    l_run += __shfl_xor_sync(0xffffffffu, l_run, 2);
+    if (g < G) {
 #pragma unroll
-    for (int g = 0; g < GH; ++g) {
-      const float m_o = __shfl_xor_sync(0xffffffffu, m[g], 16);
-      const float l_o = __shfl_xor_sync(0xffffffffu, l[g], 16);
-      const float mm = fmaxf(m[g], m_o);
-      const float mu = (mm == -INFINITY) ? 0.f : mm;
-      // evaluate in a half-independent order so both halves hold identical values
-      const float c_lo = exp2f((half ? m_o : m[g]) - mu);
-      const float c_hi = exp2f((half ? m[g] : m_o) - mu);
-      const float l_lo = half ? l_o : l[g], l_hi = half ? l[g] : l_o;
-      l[g] = l_lo * c_lo + l_hi * c_hi;
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const float a_o = __shfl_xor_sync(0xffffffffu, acc[g][i], 16);
-        const float a_lo = half ? a_o : acc[g][i], a_hi = half ? acc[g][i] : a_o;
-        acc[g][i] = a_lo * c_lo + a_hi * c_hi;
+      for (int j = 0; j < 16; ++j) {
+        sm_acc[warp][g][16 * (2 * t) + j] = o[j][0];
+        sm_acc[warp][g][16 * (2 * t + 1) + j] = o[j][1];
       }
-      m[g] = mm;
-      if (half == 0) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) sm_acc[warp][g][8 * dl + i] = acc[g][i];
-        if (dl == 0) {
-          sm_m[warp][g] = m[g];
-          sm_l[warp][g] = l[g];
-        }
+      if (t == 0) {
+        sm_m[warp][g] = m_run;
+        sm_l[warp][g] = l_run;
       }
     }
     __syncthreads();
     const int tid = threadIdx.x;
 #pragma unroll
-    for (int g = 0; g < GH; ++g) {
-      float mm = fmaxf(fmaxf(sm_m[0][g], sm_m[1][g]), fmaxf(sm_m[2][g], sm_m[3][g]));
+    for (int gg = 0; gg < G; ++gg) {
+      float mm = fmaxf(fmaxf(sm_m[0][gg], sm_m[1][gg]), fmaxf(sm_m[2][gg], sm_m[3][gg]));
       const float mu = (mm == -INFINITY) ? 0.f : mm;
-      float o = 0.f, ll = 0.f;
+      float oo = 0.f, ll = 0.f;
 #pragma unroll
       for (int w = 0; w < 4; ++w) {
-        const float c = exp2f(sm_m[w][g] - mu);
-        o += sm_acc[w][g][tid] * c;
-        ll += sm_l[w][g] * c;
+        const float c = exp2f(sm_m[w][gg] - mu);
+        oo += sm_acc[w][gg][tid] * c;
+        ll += sm_l[w][gg] * c;
       }
-      const long long idx = (static_cast<long long>(b) * n_heads + head0 + g) * max_splits + split;
-      scratch_o[idx * 128 + tid] = o;
+      const long long idx = (static_cast<long long>(b) * n_heads + head0 + gg) * max_splits + split;
+      scratch_o[idx * 128 + tid] = oo;
       if (tid == 0) {
         scratch_ml[idx * 2] = mm;
         scratch_ml[idx * 2 + 1] = ll;
@@ -206,13 +217,13 @@ decode_attn_merge_kernel(const float* __restrict__ scratch_o, const float* __res
   out[(static_cast<long long>(b) * n_heads + head) * 128 + tid] = __float2bfloat16_rn(r);
 }
 
-template <int G, int GH>
+template <int G>
 static int launch_decode(const void* q, const void* kv_cache, const int* block_table,
                          int max_blocks, const int* seq_lens, float* scratch_o, float* scratch_ml,
                          int B, int n_heads, int n_kv_heads, int max_splits, float scale,
                          cudaStream_t stream) {
-  dim3 grid(max_splits, n_heads / GH, B);
-  BCG_CUDA_CHECK(launch_k(decode_attn_kernel<G, GH>, grid, dim3(128), 0, stream,
+  dim3 grid(max_splits, n_kv_heads, B);
+  BCG_CUDA_CHECK(launch_k(decode_attn_kernel<G>, grid, dim3(128), 0, stream,
                           reinterpret_cast<const __nv_bfloat16*>(q),
                           reinterpret_cast<const __nv_bfloat16*>(kv_cache), block_table, max_blocks,
                           seq_lens, scratch_o, scratch_ml, n_heads, n_kv_heads, max_splits,
@@ -235,20 +246,22 @@ int decode_attn_paged(const void* q, const void* kv_cache, const int* block_tabl
   }
   const int G = n_heads / n_kv_heads;
   int rc;
-#define BCG_DECODE_CASE(g, gh)                                                                   \
-  case g:                                                                                        \
-    rc = launch_decode<g, gh>(q, kv_cache, block_table, max_blocks_per_seq, seq_lens, scratch_o, \
-                              scratch_ml, B, n_heads, n_kv_heads, max_splits, scale, stream);    \
+#define BCG_DECODE_CASE(g)                                                                    \
+  case g:                                                                                     \
+    rc = launch_decode<g>(q, kv_cache, block_table, max_blocks_per_seq, seq_lens, scratch_o,  \
+                          scratch_ml, B, n_heads, n_kv_heads, max_splits, scale, stream);     \
     break;
   switch (G) {
-    BCG_DECODE_CASE(1, 1)
-    BCG_DECODE_CASE(2, 2)
-    BCG_DECODE_CASE(4, 4)
-    BCG_DECODE_CASE(5, 5)
-    BCG_DECODE_CASE(6, 3)
-    BCG_DECODE_CASE(8, 4)
+    BCG_DECODE_CASE(1)
+    BCG_DECODE_CASE(2)
+    BCG_DECODE_CASE(3)
+    BCG_DECODE_CASE(4)
+    BCG_DECODE_CASE(5)
+    BCG_DECODE_CASE(6)
+    BCG_DECODE_CASE(7)
+    BCG_DECODE_CASE(8)
     default:
-      set_last_error("bcg_decode_attn_paged", "unsupported GQA group size (1,2,4,5,6,8)");
+      set_last_error("bcg_decode_attn_paged", "unsupported GQA group size (1..8)");
       return BCG_ERR_UNSUPPORTED;
   }
 #undef BCG_DECODE_CASE
