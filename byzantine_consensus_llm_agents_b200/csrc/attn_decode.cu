@@ -9,7 +9,8 @@
 //          tensor-core fragments (16 loads in flight per lane), QK^T and PV on m16n8k16 bf16
 //          MMAs, online softmax in fp32, partial (m, l, o[128]) per (row, head, chunk) to
 //          scratch.
-// Phase 2  decode_attn_merge_kernel  grid (n_heads, B): fixed-order merge of the chunks.
+// Phase 2  (same kernel) the chunk CTA that finishes last — found with one atomic counter per
+//          (row, KV head) that it resets to zero — merges all chunks in chunk order.
 //
 // KV cache layout (one layer): [page][2 (k,v)][n_kv_heads][16 tokens][128] bf16 — a
 // (page, kv-head) K or V slab is 4 KB contiguous.
@@ -23,13 +24,16 @@ namespace bcg {
 constexpr int kSplitTokens = 256;
 constexpr int kPage = 16;
 
-__device__ __forceinline__ void mma_bf16_16816(float* c, uint32_t a0, uint32_t a1, uint32_t a2,
-                                               uint32_t a3, uint32_t b0, uint32_t b1) {
+// Rows 8..15 of every product are zero padding: their A registers are 0, their accumulator
+// inputs are 0 and their outputs land in write-only dummies, so they cost no live registers.
+__device__ __forceinline__ void mma_top8(float& c0, float& c1, uint32_t a0, uint32_t a2, uint32_t b0,
+                                         uint32_t b1) {
+  float d2, d3;
   asm volatile(
-      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, "
-      "{%8, %9}, {%0, %1, %2, %3};"
-      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %8, %5, %8}, "
+      "{%6, %7}, {%0, %1, %9, %9};"
+      : "+f"(c0), "+f"(c1), "=f"(d2), "=f"(d3)
+      : "r"(a0), "r"(a2), "r"(b0), "r"(b1), "r"(0u), "f"(0.f));
 }
 
 // G = q-heads per KV head (1..8).  One CTA = one (row, KV head, 256-token chunk); each of the 4
@@ -46,15 +50,17 @@ __device__ __forceinline__ void mma_bf16_16816(float* c, uint32_t a0, uint32_t a
 //               interleaves them pairwise (PRMT) into B fragments; output column g of MMA n-tile
 //               j is head dim 16g + j.
 template <int G>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 4)
 decode_attn_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ kv_cache,
                    const int* __restrict__ block_table, int max_blocks,
                    const int* __restrict__ seq_lens, float* __restrict__ scratch_o,
-                   float* __restrict__ scratch_ml, int n_heads, int n_kv_heads, int max_splits,
+                   float* __restrict__ scratch_ml, int* __restrict__ counters,
+                   __nv_bfloat16* __restrict__ out, int n_heads, int n_kv_heads, int max_splits,
                    float scale_log2e) {
   __shared__ float sm_acc[4][G][128];
   __shared__ float sm_m[4][G];
   __shared__ float sm_l[4][G];
+  __shared__ int sm_last;
   pdl_launch_dependents();
   pdl_wait();
   const int split = blockIdx.x;
@@ -81,9 +87,9 @@ decode_attn_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __r
       qa[2 * j][0] = raw.x; qa[2 * j][1] = raw.y;
       qa[2 * j + 1][0] = raw.z; qa[2 * j + 1][1] = raw.w;
     }
-    float o[16][4];
+    float o[16][2];
 #pragma unroll
-    for (int j = 0; j < 16; ++j) o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f;
+    for (int j = 0; j < 16; ++j) o[j][0] = o[j][1] = 0.f;
     float m_run = -INFINITY, l_run = 0.f;  // row g (replicated over the quad; l is a quad-partial)
 
     for (int pg = tok0 / kPage + warp; pg * kPage < tok1; pg += 4) {
@@ -103,14 +109,14 @@ decode_attn_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __r
         vf[i][1] = ldg_nc_v4(vbase + vt[i] * 128 + 16 * g + 8);
       }
       // ---- S = Q K^T
-      float s[2][4];
+      float s[2][2];
 #pragma unroll
       for (int nt = 0; nt < 2; ++nt) {
-        s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+        s[nt][0] = s[nt][1] = 0.f;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          mma_bf16_16816(s[nt], qa[2 * j][0], 0u, qa[2 * j][1], 0u, kf[nt][j].x, kf[nt][j].y);
-          mma_bf16_16816(s[nt], qa[2 * j + 1][0], 0u, qa[2 * j + 1][1], 0u, kf[nt][j].z, kf[nt][j].w);
+          mma_top8(s[nt][0], s[nt][1], qa[2 * j][0], qa[2 * j][1], kf[nt][j].x, kf[nt][j].y);
+          mma_top8(s[nt][0], s[nt][1], qa[2 * j + 1][0], qa[2 * j + 1][1], kf[nt][j].z, kf[nt][j].w);
         }
       }
       // ---- online softmax of row g over this page's 16 tokens (this lane: tokens vt[0..3])
@@ -155,7 +161,7 @@ decode_attn_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __r
         const uint32_t* v3 = reinterpret_cast<const uint32_t*>(&vf[3][h]);
         const uint32_t b0 = __byte_perm(v0[w], v1[w], sel);
         const uint32_t b1 = __byte_perm(v2[w], v3[w], sel);
-        mma_bf16_16816(o[j], pa0, 0u, pa2, 0u, b0, b1);
+        mma_top8(o[j][0], o[j][1], pa0, pa2, b0, b1);
       }
     }
     l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
@@ -191,50 +197,58 @@ decode_attn_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __r
         scratch_ml[idx * 2 + 1] = ll;
       }
     }
+    // ---- the chunk that finishes last merges all chunks of this (row, KV head), always in chunk
+    // order, so the result does not depend on which CTA happens to be last
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+      const int prev = atomicAdd(&counters[b * n_kv_heads + kvh], 1);
+      sm_last = (prev == n_splits - 1);
+    }
+    __syncthreads();
+    if (sm_last) {
+      __threadfence();
+#pragma unroll
+      for (int gg = 0; gg < G; ++gg) {
+        const long long base = (static_cast<long long>(b) * n_heads + head0 + gg) * max_splits;
+        float mm = -INFINITY;
+        for (int sp = 0; sp < n_splits; ++sp) mm = fmaxf(mm, __ldcg(&scratch_ml[(base + sp) * 2]));
+        const float mu = (mm == -INFINITY) ? 0.f : mm;
+        float oo = 0.f, ll = 0.f;
+        for (int sp = 0; sp < n_splits; ++sp) {
+          const float c = exp2f(__ldcg(&scratch_ml[(base + sp) * 2]) - mu);
+          oo += __ldcg(&scratch_o[(base + sp) * 128 + tid]) * c;
+          ll += __ldcg(&scratch_ml[(base + sp) * 2 + 1]) * c;
+        }
+        out[(static_cast<long long>(b) * n_heads + head0 + gg) * 128 + tid] =
+            __float2bfloat16_rn(ll > 0.f ? oo / ll : 0.f);
+      }
+      if (tid == 0) counters[b * n_kv_heads + kvh] = 0;  // leave the counters zero for the next call
+    }
   }
-}
-
-__global__ void __launch_bounds__(128)
-decode_attn_merge_kernel(const float* __restrict__ scratch_o, const float* __restrict__ scratch_ml,
-                         const int* __restrict__ seq_lens, __nv_bfloat16* __restrict__ out,
-                         int n_heads, int max_splits) {
-  pdl_launch_dependents();
-  pdl_wait();
-  const int head = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
-  const int seq_len = seq_lens[b];
-  const int n_splits = (seq_len + kSplitTokens - 1) / kSplitTokens;
-  const long long base = (static_cast<long long>(b) * n_heads + head) * max_splits;
-  float mm = -INFINITY;
-  for (int s = 0; s < n_splits; ++s) mm = fmaxf(mm, scratch_ml[(base + s) * 2]);
-  const float mu = (mm == -INFINITY) ? 0.f : mm;
-  float o = 0.f, ll = 0.f;
-  for (int s = 0; s < n_splits; ++s) {
-    const float c = exp2f(scratch_ml[(base + s) * 2] - mu);
-    o += scratch_o[(base + s) * 128 + tid] * c;
-    ll += scratch_ml[(base + s) * 2 + 1] * c;
-  }
-  const float r = ll > 0.f ? o / ll : 0.f;
-  out[(static_cast<long long>(b) * n_heads + head) * 128 + tid] = __float2bfloat16_rn(r);
 }
 
 template <int G>
 static int launch_decode(const void* q, const void* kv_cache, const int* block_table,
                          int max_blocks, const int* seq_lens, float* scratch_o, float* scratch_ml,
-                         int B, int n_heads, int n_kv_heads, int max_splits, float scale,
-                         cudaStream_t stream) {
+                         int* counters, void* out, int B, int n_heads, int n_kv_heads,
+                         int max_splits, float scale, cudaStream_t stream) {
   dim3 grid(max_splits, n_kv_heads, B);
   BCG_CUDA_CHECK(launch_k(decode_attn_kernel<G>, grid, dim3(128), 0, stream,
                           reinterpret_cast<const __nv_bfloat16*>(q),
                           reinterpret_cast<const __nv_bfloat16*>(kv_cache), block_table, max_blocks,
-                          seq_lens, scratch_o, scratch_ml, n_heads, n_kv_heads, max_splits,
+                          seq_lens, scratch_o, scratch_ml, counters,
+                          reinterpret_cast<__nv_bfloat16*>(out), n_heads, n_kv_heads, max_splits,
                           scale * 1.4426950408889634f));
   return BCG_OK;
 }
 
+// `counters`: B * n_kv_heads ints, zero on entry, zero again on exit; nullptr = the ints that
+// follow scratch_ml's B * n_heads * max_splits * 2 floats (the public entry point's layout).
 int decode_attn_paged(const void* q, const void* kv_cache, const int* block_table,
                       int max_blocks_per_seq, const int* seq_lens, void* out, float* scratch_o,
-                      float* scratch_ml, int B, int n_heads, int n_kv_heads, int page_size,
-                      int max_splits, float scale, cudaStream_t stream) {
+                      float* scratch_ml, int* counters, int B, int n_heads, int n_kv_heads,
+                      int page_size, int max_splits, float scale, cudaStream_t stream) {
   if (!q || !kv_cache || !block_table || !seq_lens || !out || !scratch_o || !scratch_ml || B <= 0 ||
       n_heads <= 0 || n_kv_heads <= 0 || max_splits <= 0 || (n_heads % n_kv_heads)) {
     set_last_error("bcg_decode_attn_paged", "bad argument");
@@ -245,11 +259,15 @@ int decode_attn_paged(const void* q, const void* kv_cache, const int* block_tabl
     return BCG_ERR_UNSUPPORTED;
   }
   const int G = n_heads / n_kv_heads;
+  if (!counters) {
+    counters = reinterpret_cast<int*>(scratch_ml + static_cast<long long>(B) * n_heads * max_splits * 2);
+  }
   int rc;
 #define BCG_DECODE_CASE(g)                                                                    \
   case g:                                                                                     \
     rc = launch_decode<g>(q, kv_cache, block_table, max_blocks_per_seq, seq_lens, scratch_o,  \
-                          scratch_ml, B, n_heads, n_kv_heads, max_splits, scale, stream);     \
+                          scratch_ml, counters, out, B, n_heads, n_kv_heads, max_splits,      \
+                          scale, stream);                                                     \
     break;
   switch (G) {
     BCG_DECODE_CASE(1)
@@ -266,9 +284,6 @@ int decode_attn_paged(const void* q, const void* kv_cache, const int* block_tabl
   }
 #undef BCG_DECODE_CASE
   if (rc != BCG_OK) return rc;
-  BCG_CUDA_CHECK(launch_k(decode_attn_merge_kernel, dim3(n_heads, B), dim3(128), 0, stream,
-                          static_cast<const float*>(scratch_o), static_cast<const float*>(scratch_ml),
-                          seq_lens, reinterpret_cast<__nv_bfloat16*>(out), n_heads, max_splits));
   return BCG_OK;
 }
 
@@ -285,24 +300,28 @@ int decode_attn_paged(const void* q, const void* kv_cache, const int* block_tabl
 // array below; the caller still passes q, the KV cache, the block table, seq_lens and out.
 //
 //   * Limit: B * n_heads * max_splits * 130 floats <= kStaticScratchFloats (4 Mi floats =
-//     16 MiB).  Larger problems are refused with BCG_STATUS_TOO_LARGE; use
+//     16 MiB) and B * n_kv_heads <= 4096.  Larger problems are refused with BCG_STATUS_TOO_LARGE; use
 //     bcg_decode_attn_paged with caller-owned scratch instead.
 //   * Cost: every GPU that loads the library keeps these 16 MiB until the process exits.
 //   * The first call on each device looks the array's device address up
 //     (cudaGetSymbolAddress with that device current) and caches it; make that first call
 //     before any stream capture begins.  Later calls only launch kernels.
 //   * All calls on a device share the one array, and it keeps whatever the previous call left
-//     in it.  Nothing has to be cleared: phase 1 writes every (row, head, chunk) entry that
-//     phase 2 reads in the same call, and entries of chunks beyond a row's length are never
-//     read.  For the same reason two calls that overlap on the GPU (different streams) race on
-//     the array — issue them on one stream, or order them with events.
+//     in it.  The partial results need no clearing: every (row, head, chunk) entry is written
+//     before it is read in the same call, and entries of chunks beyond a row's length are never
+//     read.  The per-(row, KV head) chunk counters DO have to start at zero; they live in a fixed
+//     region of their own (so partial results of another shape never land on them), start out
+//     zero like all static device memory, and each call puts every counter it used back to zero.
+//     For the same reason two calls that overlap on the GPU (different streams) race on the
+//     array — issue them on one stream, or order them with events.
 // ---------------------------------------------------------------------------------------
 constexpr long long kStaticScratchFloats = 4ll * 1024 * 1024;
+constexpr int kStaticCounters = 4096;
 constexpr int kMaxDevices = 64;
 
 // NOTE: in host code this name is only a host-side handle for the symbol, never a device
 // address; the device address is obtained once per device below.
-static __device__ __align__(256) float g_decode_scratch[kStaticScratchFloats];
+static __device__ __align__(256) float g_decode_scratch[kStaticScratchFloats + kStaticCounters];
 
 static std::mutex g_scratch_mu;
 static float* g_scratch_addr[kMaxDevices] = {};
@@ -334,7 +353,7 @@ int decode_attn_paged_static(const void* q, const void* kv_cache, const int* blo
   }
   const long long n_o = static_cast<long long>(B) * n_heads * max_splits * 128;
   const long long n_ml = static_cast<long long>(B) * n_heads * max_splits * 2;
-  if (n_o + n_ml > kStaticScratchFloats) {
+  if (n_o + n_ml > kStaticScratchFloats || static_cast<long long>(B) * n_kv_heads > kStaticCounters) {
     set_last_error("bcg_decode_attn_paged_static",
                    "B * n_heads * max_splits * 130 floats exceeds the built-in 16 MiB scratch; "
                    "use bcg_decode_attn_paged with caller-owned scratch");
@@ -344,8 +363,8 @@ int decode_attn_paged_static(const void* q, const void* kv_cache, const int* blo
   const int rc = static_scratch_on_current_device(&scratch);
   if (rc != BCG_OK) return rc;
   return decode_attn_paged(q, kv_cache, block_table, max_blocks_per_seq, seq_lens, out, scratch,
-                           scratch + n_o, B, n_heads, n_kv_heads, page_size, max_splits, scale,
-                           stream);
+                           scratch + n_o, reinterpret_cast<int*>(scratch + kStaticScratchFloats), B,
+                           n_heads, n_kv_heads, page_size, max_splits, scale, stream);
 }
 
 }  // namespace bcg

@@ -78,7 +78,7 @@ int bcg_decode_attn_paged(const void* q, const void* kv_cache, const int* block_
                           float* scratch_ml, int B, int n_heads, int n_kv_heads, int page_size,
                           int max_splits, float scale, void* stream) {
   return decode_attn_paged(q, kv_cache, block_table, max_blocks_per_seq, seq_lens, out, scratch_o,
-                           scratch_ml, B, n_heads, n_kv_heads, page_size, max_splits, scale,
+                           scratch_ml, nullptr, B, n_heads, n_kv_heads, page_size, max_splits, scale,
                            S(stream));
 }
 

@@ -27,8 +27,8 @@ int swiglu_reduce(const float* partials, int n_partials, long long partial_strid
 
 int decode_attn_paged(const void* q, const void* kv_cache, const int* block_table,
                       int max_blocks_per_seq, const int* seq_lens, void* out, float* scratch_o,
-                      float* scratch_ml, int B, int n_heads, int n_kv_heads, int page_size,
-                      int max_splits, float scale, cudaStream_t stream);
+                      float* scratch_ml, int* counters, int B, int n_heads, int n_kv_heads,
+                      int page_size, int max_splits, float scale, cudaStream_t stream);
 int decode_attn_paged_static(const void* q, const void* kv_cache, const int* block_table,
                              int max_blocks_per_seq, const int* seq_lens, void* out, int B,
                              int n_heads, int n_kv_heads, int page_size, int max_splits, float scale,

@@ -115,8 +115,8 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
                                 m->k_norm ? m->k_norm[l] : nullptr, m->cos_sin, positions, slot_map,
                                 ws->q, m->kv_cache[l], B, hq, hkv, m->page_size, m->rms_eps, st));
     BCG_TRY(decode_attn_paged(ws->q, m->kv_cache[l], block_table, max_blocks, seq_lens, ws->attn,
-                              ws->attn_scratch_o, ws->attn_scratch_ml, B, hq, hkv, m->page_size,
-                              ws->max_splits, scale, st));
+                              ws->attn_scratch_o, ws->attn_scratch_ml, nullptr, B, hq, hkv,
+                              m->page_size, ws->max_splits, scale, st));
     BCG_TRY(gemm_bf16_tn(ws->attn, m->w_o[l], P, B, d, hq * 128, hq * 128, hq * 128, d, BCG_EPI_F32,
                          s_o, gf, st));
     BCG_TRY(add_rmsnorm(ws->residual, P, 1, s_o, static_cast<long long>(B) * d, m->ln2[l], ws->xn,

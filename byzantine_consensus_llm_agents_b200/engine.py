@@ -176,7 +176,7 @@ class Engine:
             residual=z(T, d, dt=f32), xn=z(T, d), qkv=z(T, cfg.qkv_dim, dt=f32), q=z(T, cfg.n_heads * 128),
             attn=z(T, cfg.n_heads * 128), act=z(T, cfg.d_ff), delta=z(T, d, dt=f32), partials=z(pf, dt=f32),
             so=z(B * cfg.n_heads * self.max_splits_cap * 128, dt=f32),
-            sml=z(B * cfg.n_heads * self.max_splits_cap * 2, dt=f32),
+            sml=z(B * cfg.n_heads * self.max_splits_cap * 2 + B * cfg.n_kv_heads, dt=f32),  # + chunk counters
             logits=z(B, cfg.vocab, dt=f32), xn_last=z(B, d))
         ws = L.Workspace()
         b = self.buf
@@ -286,7 +286,7 @@ class Engine:
     def launches_per_decode_step(self, B: int) -> int:
         cfg = self.cfg
         s_gu = L.splits_for(B, 2 * cfg.d_ff, cfg.d_model)
-        per_layer = 9 + (1 if s_gu > 1 else 0)   # norm, qkv, rope, attn, merge, o, norm, gate_up(+reduce), down
+        per_layer = 8 + (1 if s_gu > 1 else 0)   # norm, qkv, rope, attn, o, norm, gate_up(+reduce), down
         return cfg.n_layers * per_layer + 2 + 2  # final norm + lm_head + sampler + active count
 
     def _graph_for(self, B: int, max_splits: int, use_forced: bool):

@@ -87,6 +87,7 @@ class B200LLM:
             seed = int(model_config.get("weight_seed", os.environ.get("BCG_B200_WEIGHT_SEED", 0)))
             factory = lambda c, dev: M.Weights.random_init(c, dev, seed=seed)
         device = model_config.get("device", "cuda:0")
+        self.data_parallel = bool(model_config.get("data_parallel", False))
         self.cfg = cfg
         self.tokenizer = get_tokenizer(cfg.family, cfg.vocab)
         weights = factory(cfg, torch.device(device))
@@ -103,9 +104,22 @@ class B200LLM:
 
     def run(self, prompts: List[str], schemas: List[Optional[dict]], temperature: float,
             max_tokens: int) -> List[str]:
-        from .engine import Request
-        reqs = [Request(p, s, float(temperature), int(max_tokens)) for p, s in zip(prompts, schemas)]
-        return [r.text for r in self.engine.generate(reqs)]
+        from . import dp
+        from .engine import Request, row_seed
+        call = self.engine.calls
+        if not self.data_parallel or dp.dist_info()[1] == 1:
+            reqs = [Request(p, s, float(temperature), int(max_tokens)) for p, s in zip(prompts, schemas)]
+            return [r.text for r in self.engine.generate(reqs)]
+
+        # rows of this call are split over the replicas; each row keeps the Philox key of its
+        # GLOBAL index, so the gathered texts equal what one GPU would have produced
+        def run_local(rows):
+            reqs = [Request(prompts[i], schemas[i], float(temperature), int(max_tokens),
+                            seed=row_seed(self.engine.base_seed, call, i)) for i in rows]
+            return [r.text for r in self.engine.generate(reqs)]
+        texts = dp.run_sharded(run_local, len(prompts))
+        self.engine.calls = call + 1          # replicas with no rows still advance the call counter
+        return texts
 
     def close(self) -> None:
         self.engine.close()

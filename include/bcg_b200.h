@@ -88,8 +88,10 @@ int bcg_swiglu_reduce(const float* partials, int n_partials, long long partial_s
                       int T, int two_f, void* stream);
 
 /* One query token per row over the paged KV cache (GQA, head_dim 128, page_size 16).
- * seq_lens[b] counts the current token.  scratch_o: B*n_heads*max_splits*128 floats,
- * scratch_ml: B*n_heads*max_splits*2 floats; max_splits >= ceil(max seq_len / 256).
+ * seq_lens[b] counts the current token.  scratch_o: B*n_heads*max_splits*128 floats;
+ * scratch_ml: B*n_heads*max_splits*2 floats followed by B*n_kv_heads int32 chunk counters that
+ * must be ZERO before the first call (the kernel leaves them zero); max_splits >=
+ * ceil(max seq_len / 256).
  * Stands in for the FlashInfer paged decode kernel vLLM dispatches on sm_100. */
 int bcg_decode_attn_paged(const void* q, const void* kv_cache, const int* block_table,
                           int max_blocks_per_seq, const int* seq_lens, void* out, float* scratch_o,
@@ -102,10 +104,11 @@ int bcg_decode_attn_paged(const void* q, const void* kv_cache, const int* block_
  * a server whose whole device budget already went to weights and KV pages, or a decode loop that
  * must avoid cudaMalloc/cudaFree because they synchronise the device.  The scratch is a 16 MiB
  * array inside the library (held by every GPU that loads it, until exit), so the problem must
- * satisfy B * n_heads * max_splits * 130 <= 4 * 1024 * 1024 floats; larger calls return
- * BCG_STATUS_TOO_LARGE.  The first call on a device resolves the array's address — make it
+ * satisfy B * n_heads * max_splits * 130 <= 4 * 1024 * 1024 floats and B * n_kv_heads <= 4096;
+ * larger calls return BCG_STATUS_TOO_LARGE.  The first call on a device resolves the array's address — make it
  * before any stream capture.  Calls share the array: keep them on one stream (overlapping calls
- * race); nothing needs clearing between calls.  Allocates nothing, frees nothing. */
+ * race); the caller never has to clear anything (the chunk counters inside start at zero and every
+ * call returns them to zero).  Allocates nothing, frees nothing. */
 int bcg_decode_attn_paged_static(const void* q, const void* kv_cache, const int* block_table,
                                  int max_blocks_per_seq, const int* seq_lens, void* out, int B,
                                  int n_heads, int n_kv_heads, int page_size, int max_splits,

@@ -346,7 +346,7 @@ def test_decode_attn_paged(H, HKV, lens):
     seq = torch.tensor(lens, device=DEV, dtype=torch.int32)
     max_splits = (max(lens) + 255) // 256 + 1
     so = torch.empty(B * H * max_splits * 128, device=DEV)
-    sml = torch.empty(B * H * max_splits * 2, device=DEV)
+    sml = torch.zeros(B * H * max_splits * 2 + B * HKV, device=DEV)  # + zeroed chunk counters
     out = torch.empty(B, H * 128, device=DEV, dtype=torch.bfloat16)
     L.check(lib.bcg_decode_attn_paged(q.data_ptr(), cache.data_ptr(), bt.data_ptr(), bt.shape[1],
                                       seq.data_ptr(), out.data_ptr(), so.data_ptr(), sml.data_ptr(), B,
@@ -372,7 +372,7 @@ def test_decode_attn_batch_invariance():
         btt = bt[rows].contiguous()
         seq = torch.tensor([lens[r] for r in rows], device=DEV, dtype=torch.int32)
         so = torch.empty(B * H * max_splits * 128, device=DEV)
-        sml = torch.empty(B * H * max_splits * 2, device=DEV)
+        sml = torch.zeros(B * H * max_splits * 2 + B * HKV, device=DEV)  # + zeroed chunk counters
         out = torch.empty(B, H * 128, device=DEV, dtype=torch.bfloat16)
         L.check(lib.bcg_decode_attn_paged(qq.data_ptr(), cache.data_ptr(), btt.data_ptr(), btt.shape[1],
                                           seq.data_ptr(), out.data_ptr(), so.data_ptr(), sml.data_ptr(),

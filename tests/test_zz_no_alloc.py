@@ -49,7 +49,7 @@ def _run_both(lib, lens, H, HKV, seed):
     scale = 1.0 / math.sqrt(128)
     # existing entry point: caller-owned scratch
     so = torch.empty(B * H * max_splits * 128, device=DEV)
-    sml = torch.empty(B * H * max_splits * 2, device=DEV)
+    sml = torch.zeros(B * H * max_splits * 2 + B * HKV, device=DEV)  # + zeroed chunk counters
     want = torch.empty(B, H * 128, device=DEV, dtype=torch.bfloat16)
     L.check(lib.bcg_decode_attn_paged(q.data_ptr(), cache.data_ptr(), bt.data_ptr(), bt.shape[1],
                                       seq.data_ptr(), want.data_ptr(), so.data_ptr(), sml.data_ptr(), B,
