@@ -243,13 +243,13 @@ static int launch_decode(const void* q, const void* kv_cache, const int* block_t
   return BCG_OK;
 }
 
-// `counters`: B * n_kv_heads ints, zero on entry, zero again on exit; nullptr = the ints that
-// follow scratch_ml's B * n_heads * max_splits * 2 floats (the public entry point's layout).
+// `counters`: B * n_kv_heads ints, zero on entry, zero again on exit.
 int decode_attn_paged(const void* q, const void* kv_cache, const int* block_table,
                       int max_blocks_per_seq, const int* seq_lens, void* out, float* scratch_o,
                       float* scratch_ml, int* counters, int B, int n_heads, int n_kv_heads,
                       int page_size, int max_splits, float scale, cudaStream_t stream) {
-  if (!q || !kv_cache || !block_table || !seq_lens || !out || !scratch_o || !scratch_ml || B <= 0 ||
+  if (!q || !kv_cache || !block_table || !seq_lens || !out || !scratch_o || !scratch_ml || !counters ||
+      B <= 0 ||
       n_heads <= 0 || n_kv_heads <= 0 || max_splits <= 0 || (n_heads % n_kv_heads)) {
     set_last_error("bcg_decode_attn_paged", "bad argument");
     return BCG_ERR_ARG;
@@ -259,9 +259,6 @@ int decode_attn_paged(const void* q, const void* kv_cache, const int* block_tabl
     return BCG_ERR_UNSUPPORTED;
   }
   const int G = n_heads / n_kv_heads;
-  if (!counters) {
-    counters = reinterpret_cast<int*>(scratch_ml + static_cast<long long>(B) * n_heads * max_splits * 2);
-  }
   int rc;
 #define BCG_DECODE_CASE(g)                                                                    \
   case g:                                                                                     \

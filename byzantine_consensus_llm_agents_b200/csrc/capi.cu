@@ -75,11 +75,11 @@ int bcg_swiglu_reduce(const float* partials, int n_partials, long long partial_s
 
 int bcg_decode_attn_paged(const void* q, const void* kv_cache, const int* block_table,
                           int max_blocks_per_seq, const int* seq_lens, void* out, float* scratch_o,
-                          float* scratch_ml, int B, int n_heads, int n_kv_heads, int page_size,
-                          int max_splits, float scale, void* stream) {
+                          float* scratch_ml, int* chunk_counters, int B, int n_heads, int n_kv_heads,
+                          int page_size, int max_splits, float scale, void* stream) {
   return decode_attn_paged(q, kv_cache, block_table, max_blocks_per_seq, seq_lens, out, scratch_o,
-                           scratch_ml, nullptr, B, n_heads, n_kv_heads, page_size, max_splits, scale,
-                           S(stream));
+                           scratch_ml, chunk_counters, B, n_heads, n_kv_heads, page_size, max_splits,
+                           scale, S(stream));
 }
 
 int bcg_decode_attn_paged_static(const void* q, const void* kv_cache, const int* block_table,

@@ -72,7 +72,7 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
                  int B, int flags, cudaStream_t st) {
   BCG_TRY(check_model(m, ws));
   if (B <= 0 || B > ws->B_max || B > 128 || !ws->partials || !ws->attn_scratch_o ||
-      !ws->attn_scratch_ml) {
+      !ws->attn_scratch_ml || !ws->attn_counters) {
     set_last_error("bcg_model_decode", "B exceeds the workspace (or 128), or decode scratch missing");
     return BCG_ERR_TOO_LARGE;
   }
@@ -115,7 +115,7 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
                                 m->k_norm ? m->k_norm[l] : nullptr, m->cos_sin, positions, slot_map,
                                 ws->q, m->kv_cache[l], B, hq, hkv, m->page_size, m->rms_eps, st));
     BCG_TRY(decode_attn_paged(ws->q, m->kv_cache[l], block_table, max_blocks, seq_lens, ws->attn,
-                              ws->attn_scratch_o, ws->attn_scratch_ml, nullptr, B, hq, hkv,
+                              ws->attn_scratch_o, ws->attn_scratch_ml, ws->attn_counters, B, hq, hkv,
                               m->page_size, ws->max_splits, scale, st));
     BCG_TRY(gemm_bf16_tn(ws->attn, m->w_o[l], P, B, d, hq * 128, hq * 128, hq * 128, d, BCG_EPI_F32,
                          s_o, gf, st));

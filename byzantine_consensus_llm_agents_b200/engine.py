@@ -176,7 +176,8 @@ class Engine:
             residual=z(T, d, dt=f32), xn=z(T, d), qkv=z(T, cfg.qkv_dim, dt=f32), q=z(T, cfg.n_heads * 128),
             attn=z(T, cfg.n_heads * 128), act=z(T, cfg.d_ff), delta=z(T, d, dt=f32), partials=z(pf, dt=f32),
             so=z(B * cfg.n_heads * self.max_splits_cap * 128, dt=f32),
-            sml=z(B * cfg.n_heads * self.max_splits_cap * 2 + B * cfg.n_kv_heads, dt=f32),  # + chunk counters
+            sml=z(B * cfg.n_heads * self.max_splits_cap * 2, dt=f32),
+            attn_counters=z(B * cfg.n_kv_heads, dt=i32),
             logits=z(B, cfg.vocab, dt=f32), xn_last=z(B, d))
         ws = L.Workspace()
         b = self.buf
@@ -184,6 +185,7 @@ class Engine:
         ws.attn, ws.act, ws.delta = b["attn"].data_ptr(), b["act"].data_ptr(), b["delta"].data_ptr()
         ws.partials, ws.partials_floats = b["partials"].data_ptr(), pf
         ws.attn_scratch_o, ws.attn_scratch_ml = b["so"].data_ptr(), b["sml"].data_ptr()
+        ws.attn_counters = b["attn_counters"].data_ptr()
         ws.max_splits = self.max_splits_cap
         ws.logits, ws.xn_last, ws.T_max, ws.B_max = b["logits"].data_ptr(), b["xn_last"].data_ptr(), T, B
         self.ws = ws

@@ -57,7 +57,8 @@ class Workspace(C.Structure):
     _fields_ = [
         ("residual", vp), ("xn", vp), ("qkv", vp), ("q", vp), ("attn", vp), ("act", vp),
         ("delta", vp), ("partials", vp), ("partials_floats", C.c_longlong),
-        ("attn_scratch_o", vp), ("attn_scratch_ml", vp), ("max_splits", C.c_int),
+        ("attn_scratch_o", vp), ("attn_scratch_ml", vp), ("attn_counters", vp),
+        ("max_splits", C.c_int),
         ("logits", vp), ("xn_last", vp), ("T_max", C.c_int), ("B_max", C.c_int),
     ]
 
@@ -75,7 +76,7 @@ _SIGS = {
                                           vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int,
                                           C.c_float, vp]),
     "bcg_swiglu_reduce": (C.c_int, [vp, C.c_int, C.c_longlong, vp, C.c_int, C.c_int, vp]),
-    "bcg_decode_attn_paged": (C.c_int, [vp, vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, C.c_int,
+    "bcg_decode_attn_paged": (C.c_int, [vp, vp, vp, C.c_int, vp, vp, vp, vp, vp, C.c_int, C.c_int,
                                         C.c_int, C.c_int, C.c_int, C.c_float, vp]),
     "bcg_decode_attn_paged_static": (C.c_int, [vp, vp, vp, C.c_int, vp, vp, C.c_int, C.c_int, C.c_int,
                                                C.c_int, C.c_int, C.c_float, vp]),

@@ -89,14 +89,15 @@ int bcg_swiglu_reduce(const float* partials, int n_partials, long long partial_s
 
 /* One query token per row over the paged KV cache (GQA, head_dim 128, page_size 16).
  * seq_lens[b] counts the current token.  scratch_o: B*n_heads*max_splits*128 floats;
- * scratch_ml: B*n_heads*max_splits*2 floats followed by B*n_kv_heads int32 chunk counters that
- * must be ZERO before the first call (the kernel leaves them zero); max_splits >=
- * ceil(max seq_len / 256).
+ * scratch_ml: B*n_heads*max_splits*2 floats; chunk_counters: B*n_kv_heads int32 that must be
+ * ZERO before the first call and that every call leaves zero again (keep them in a buffer of
+ * their own: partial results written by a call of another shape must never land on them);
+ * max_splits >= ceil(max seq_len / 256).
  * Stands in for the FlashInfer paged decode kernel vLLM dispatches on sm_100. */
 int bcg_decode_attn_paged(const void* q, const void* kv_cache, const int* block_table,
                           int max_blocks_per_seq, const int* seq_lens, void* out, float* scratch_o,
-                          float* scratch_ml, int B, int n_heads, int n_kv_heads, int page_size,
-                          int max_splits, float scale, void* stream);
+                          float* scratch_ml, int* chunk_counters, int B, int n_heads, int n_kv_heads,
+                          int page_size, int max_splits, float scale, void* stream);
 
 /* Same computation as bcg_decode_attn_paged, for callers that cannot allocate device memory.
  * No counterpart in the reference (the reference never manages device memory itself); it exists
@@ -204,6 +205,7 @@ typedef struct bcg_workspace {
   long long partials_floats;
   float* attn_scratch_o;
   float* attn_scratch_ml;
+  int* attn_counters;  /* int32 [B_max * n_kv_heads], zero-initialised once */
   int max_splits;
   float* logits;      /* fp32 [B_max, vocab] */
   void* xn_last;      /* bf16 [B_max, d_model] */

@@ -346,11 +346,15 @@ def test_decode_attn_paged(H, HKV, lens):
     seq = torch.tensor(lens, device=DEV, dtype=torch.int32)
     max_splits = (max(lens) + 255) // 256 + 1
     so = torch.empty(B * H * max_splits * 128, device=DEV)
-    sml = torch.zeros(B * H * max_splits * 2 + B * HKV, device=DEV)  # + zeroed chunk counters
+    sml = torch.empty(B * H * max_splits * 2, device=DEV)
+    cnt = torch.zeros(B * HKV, device=DEV, dtype=torch.int32)
     out = torch.empty(B, H * 128, device=DEV, dtype=torch.bfloat16)
-    L.check(lib.bcg_decode_attn_paged(q.data_ptr(), cache.data_ptr(), bt.data_ptr(), bt.shape[1],
-                                      seq.data_ptr(), out.data_ptr(), so.data_ptr(), sml.data_ptr(), B,
-                                      H, HKV, 16, max_splits, 1.0 / math.sqrt(128), L.stream_ptr()))
+    for _ in range(2):  # twice: the counters must come back to zero
+        L.check(lib.bcg_decode_attn_paged(q.data_ptr(), cache.data_ptr(), bt.data_ptr(), bt.shape[1],
+                                          seq.data_ptr(), out.data_ptr(), so.data_ptr(), sml.data_ptr(),
+                                          cnt.data_ptr(), B, H, HKV, 16, max_splits, 1.0 / math.sqrt(128),
+                                          L.stream_ptr()))
+    assert int(cnt.abs().sum()) == 0
     torch.cuda.synchronize()
     for b in range(B):
         ref = _attn_ref(q[b].float().view(1, H, 128), Ks[b], Vs[b], G)[0]
@@ -372,11 +376,12 @@ def test_decode_attn_batch_invariance():
         btt = bt[rows].contiguous()
         seq = torch.tensor([lens[r] for r in rows], device=DEV, dtype=torch.int32)
         so = torch.empty(B * H * max_splits * 128, device=DEV)
-        sml = torch.zeros(B * H * max_splits * 2 + B * HKV, device=DEV)  # + zeroed chunk counters
+        sml = torch.empty(B * H * max_splits * 2, device=DEV)
+        cnt = torch.zeros(B * HKV, device=DEV, dtype=torch.int32)
         out = torch.empty(B, H * 128, device=DEV, dtype=torch.bfloat16)
         L.check(lib.bcg_decode_attn_paged(qq.data_ptr(), cache.data_ptr(), btt.data_ptr(), btt.shape[1],
                                           seq.data_ptr(), out.data_ptr(), so.data_ptr(), sml.data_ptr(),
-                                          B, H, HKV, 16, max_splits, 1.0 / math.sqrt(128),
+                                          cnt.data_ptr(), B, H, HKV, 16, max_splits, 1.0 / math.sqrt(128),
                                           L.stream_ptr()))
         torch.cuda.synchronize()
         return out

@@ -49,11 +49,12 @@ def _run_both(lib, lens, H, HKV, seed):
     scale = 1.0 / math.sqrt(128)
     # existing entry point: caller-owned scratch
     so = torch.empty(B * H * max_splits * 128, device=DEV)
-    sml = torch.zeros(B * H * max_splits * 2 + B * HKV, device=DEV)  # + zeroed chunk counters
+    sml = torch.empty(B * H * max_splits * 2, device=DEV)
+    cnt = torch.zeros(B * HKV, device=DEV, dtype=torch.int32)
     want = torch.empty(B, H * 128, device=DEV, dtype=torch.bfloat16)
     L.check(lib.bcg_decode_attn_paged(q.data_ptr(), cache.data_ptr(), bt.data_ptr(), bt.shape[1],
-                                      seq.data_ptr(), want.data_ptr(), so.data_ptr(), sml.data_ptr(), B,
-                                      H, HKV, 16, max_splits, scale, L.stream_ptr()))
+                                      seq.data_ptr(), want.data_ptr(), so.data_ptr(), sml.data_ptr(),
+                                      cnt.data_ptr(), B, H, HKV, 16, max_splits, scale, L.stream_ptr()))
     # new entry point: inputs and outputs only
     got = torch.full((B, H * 128), float("nan"), device=DEV, dtype=torch.bfloat16)
     L.check(lib.bcg_decode_attn_paged_static(q.data_ptr(), cache.data_ptr(), bt.data_ptr(), bt.shape[1],

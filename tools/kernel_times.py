@@ -98,7 +98,8 @@ def main():
          B * qkv_dim * (4 * s_qkv + 2), s_qkv),
         ("decode_attn (+merge)", lambda l: L.check(lib.bcg_decode_attn_paged(
             buf["q"].data_ptr(), eng.kv_layers[l].data_ptr(), r["block_table"].data_ptr(), eng.max_blocks,
-            r["seq_lens"].data_ptr(), buf["attn"].data_ptr(), buf["so"].data_ptr(), buf["sml"].data_ptr(), B, hq, hkv,
+            r["seq_lens"].data_ptr(), buf["attn"].data_ptr(), buf["so"].data_ptr(), buf["sml"].data_ptr(),
+            buf["attn_counters"].data_ptr(), B, hq, hkv,
             16, max_splits, 1.0 / math.sqrt(128), st())), B * a.ctx * hkv * 128 * 2 * 2, max_splits),
     ]
     total = 0.0
