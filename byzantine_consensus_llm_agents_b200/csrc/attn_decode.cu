@@ -67,35 +67,47 @@ decode_attn_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __r
   const int kvh = blockIdx.y;
   const int head0 = kvh * G;
   const int b = blockIdx.z;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, t = lane & 3;
+  // Everything that does not depend on seq_len is requested up front, in parallel: the row's
+  // length, this warp's (at most 4) block-table entries and the query fragments.  Only the K/V
+  // page loads then sit on the critical path, one round trip per page.
+  const int pg0 = split * (kSplitTokens / kPage) + warp;
+  int phys[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int pg = pg0 + 4 * i;
+    phys[i] = (pg < max_blocks) ? block_table[static_cast<long long>(b) * max_blocks + pg] : 0;
+  }
+  // Q as A fragments: [k-step][a0 (k 2t,2t+1), a2 (k 8+2t,9+2t)]; rows 8..15 (a1, a3) are zero
+  uint32_t qa[8][2];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    uint4 raw = make_uint4(0u, 0u, 0u, 0u);
+    if (g < G) {
+      raw = *reinterpret_cast<const uint4*>(q + (static_cast<long long>(b) * n_heads + head0 + g) * 128 +
+                                            8 * (t + 4 * j));
+    }
+    qa[2 * j][0] = raw.x; qa[2 * j][1] = raw.y;
+    qa[2 * j + 1][0] = raw.z; qa[2 * j + 1][1] = raw.w;
+  }
   const int seq_len = seq_lens[b];
   const int n_splits = (seq_len + kSplitTokens - 1) / kSplitTokens;
   if (split < n_splits) {
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int g = lane >> 2, t = lane & 3;
     const int tok0 = split * kSplitTokens;
     const int tok1 = min(seq_len, tok0 + kSplitTokens);
 
-    // Q as A fragments: [k-step][a0 (k 2t,2t+1), a2 (k 8+2t,9+2t)]; rows 8..15 (a1, a3) are zero
-    uint32_t qa[8][2];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      uint4 raw = make_uint4(0u, 0u, 0u, 0u);
-      if (g < G) {
-        raw = *reinterpret_cast<const uint4*>(q + (static_cast<long long>(b) * n_heads + head0 + g) * 128 +
-                                              8 * (t + 4 * j));
-      }
-      qa[2 * j][0] = raw.x; qa[2 * j][1] = raw.y;
-      qa[2 * j + 1][0] = raw.z; qa[2 * j + 1][1] = raw.w;
-    }
     float o[16][2];
 #pragma unroll
     for (int j = 0; j < 16; ++j) o[j][0] = o[j][1] = 0.f;
     float m_run = -INFINITY, l_run = 0.f;  // row g (replicated over the quad; l is a quad-partial)
 
-    for (int pg = tok0 / kPage + warp; pg * kPage < tok1; pg += 4) {
-      const int phys = block_table[static_cast<long long>(b) * max_blocks + pg];
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      const int pg = pg0 + 4 * it;
+      if (pg * kPage >= tok1) break;
       const __nv_bfloat16* kbase =
-          kv_cache + ((static_cast<long long>(phys) * 2 * n_kv_heads) + kvh) * (kPage * 128);
+          kv_cache + ((static_cast<long long>(phys[it]) * 2 * n_kv_heads) + kvh) * (kPage * 128);
       const __nv_bfloat16* vbase = kbase + static_cast<long long>(n_kv_heads) * (kPage * 128);
       uint4 kf[2][4], vf[4][2];
 #pragma unroll
@@ -211,14 +223,34 @@ decode_attn_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __r
 #pragma unroll
       for (int gg = 0; gg < G; ++gg) {
         const long long base = (static_cast<long long>(b) * n_heads + head0 + gg) * max_splits;
+        // loads are issued eight chunks at a time (independent), the arithmetic stays in chunk order
         float mm = -INFINITY;
-        for (int sp = 0; sp < n_splits; ++sp) mm = fmaxf(mm, __ldcg(&scratch_ml[(base + sp) * 2]));
+        for (int s0 = 0; s0 < n_splits; s0 += 8) {
+          float mv[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) mv[k] = (s0 + k < n_splits) ? __ldcg(&scratch_ml[(base + s0 + k) * 2]) : -INFINITY;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) mm = fmaxf(mm, mv[k]);
+        }
         const float mu = (mm == -INFINITY) ? 0.f : mm;
         float oo = 0.f, ll = 0.f;
-        for (int sp = 0; sp < n_splits; ++sp) {
-          const float c = exp2f(__ldcg(&scratch_ml[(base + sp) * 2]) - mu);
-          oo += __ldcg(&scratch_o[(base + sp) * 128 + tid]) * c;
-          ll += __ldcg(&scratch_ml[(base + sp) * 2 + 1]) * c;
+        for (int s0 = 0; s0 < n_splits; s0 += 8) {
+          float mv[8], lv[8], ov[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const bool in = s0 + k < n_splits;
+            mv[k] = in ? __ldcg(&scratch_ml[(base + s0 + k) * 2]) : -INFINITY;
+            lv[k] = in ? __ldcg(&scratch_ml[(base + s0 + k) * 2 + 1]) : 0.f;
+            ov[k] = in ? __ldcg(&scratch_o[(base + s0 + k) * 128 + tid]) : 0.f;
+          }
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            if (s0 + k < n_splits) {
+              const float c = exp2f(mv[k] - mu);
+              oo += ov[k] * c;
+              ll += lv[k] * c;
+            }
+          }
         }
         out[(static_cast<long long>(b) * n_heads + head0 + gg) * 128 + tid] =
             __float2bfloat16_rn(ll > 0.f ? oo / ll : 0.f);
