@@ -4,11 +4,10 @@
 // row's arithmetic — chunk boundaries and the order partial results are merged in —
 // depends only on that row's own length, never on which other rows share the batch.
 //
-// Phase 1  decode_attn_kernel  grid (max_splits, n_kv_heads, B), 128 threads:
-//          each warp streams whole pages with 128-bit non-allocating loads straight into
-//          tensor-core fragments (16 loads in flight per lane), QK^T and PV on m16n8k16 bf16
-//          MMAs, online softmax in fp32, partial (m, l, o[128]) per (row, head, chunk) to
-//          scratch.
+// Phase 1  decode_attn_kernel  grid (max_splits, n_kv_heads, B), 160 threads:
+//          a producer warp streams the chunk's pages through an 8-stage TMA ring, four consumer
+//          warps run QK^T and PV on m16n8k16 bf16 MMAs with an fp32 online softmax, partial
+//          (m, l, o[128]) per (row, head, chunk) go to scratch.
 // Phase 2  (same kernel) the chunk CTA that finishes last — found with one atomic counter per
 //          (row, KV head) that it resets to zero — merges all chunks in chunk order.
 //
@@ -36,161 +35,212 @@ __device__ __forceinline__ void mma_top8(float& c0, float& c1, uint32_t a0, uint
       : "r"(a0), "r"(a2), "r"(b0), "r"(b1), "r"(0u), "f"(0.f));
 }
 
-// G = q-heads per KV head (1..8).  One CTA = one (row, KV head, 256-token chunk); each of the 4
-// warps walks whole pages.  Both products run on bf16 tensor-core MMAs (m16n8k16, fp32
-// accumulate) with the G query heads as MMA rows 0..G-1 (rows G..15 are zero padding — the
-// kernel is HBM-bound, the spare tensor rows cost nothing).  No shared-memory staging: a dot
-// product does not care in which order its terms are added, so the MMA k-index is PERMUTED to
-// match what a 128-bit global load delivers —
-//   S = Q K^T : lane (g,t) loads 4 x 16 B of token g's K row (dims 8(t+4j)..+7, j=0..3: the four
-//               lanes of a quad cover 64 contiguous bytes per load instruction) and feeds them as
-//               the B fragments of the 8 k-steps; Q's A fragments use the same dim order.
-//   O = P V   : lane (g,t) loads 2 x 16 B (dims 16g..16g+15) of V rows 2t, 2t+1, 8+2t, 9+2t —
-//               exactly the tokens whose probabilities it holds in its S accumulators — and
-//               interleaves them pairwise (PRMT) into B fragments; output column g of MMA n-tile
-//               j is head dim 16g + j.
+constexpr int kAttnStages = 8;                       // ring of {K page, V page} = 8 KB stages
+static_assert(kSplitTokens / kPage <= 2 * kAttnStages, "each ring stage may be used at most twice per chunk (phase parity)");
+constexpr int kAttnStageBytes = 2 * kPage * 128 * 2;  // 8192
+constexpr int kAttnThreads = 160;                     // 4 consumer warps + 1 TMA producer warp
+
+__device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
+  uint4 r;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "r"(addr));
+  return r;
+}
+
+// G = q-heads per KV head (1..8).  One CTA = one (row, KV head, 256-token chunk = 16 pages).
+//
+// Data movement: warp 4 is a TMA producer.  The layer's KV cache is described to TMA as one
+// 2-D bf16 tensor [token-rows, 128]; a page's K (or V) slab is 16 consecutive rows and arrives
+// as two 16 x 64 boxes in the 128B-swizzled layout.  The producer looks up the chunk's block-
+// table entries once and issues every page of the chunk as fast as the 8-stage ring allows, so
+// up to 64 KB per CTA (192 KB per SM at 3 CTAs) is in flight without holding a single register
+// — the kernel is bandwidth-bound, not latency-bound.
+//
+// Math: both products run on bf16 tensor-core MMAs (m16n8k16, fp32 accumulate) with the G query
+// heads as MMA rows 0..G-1 (rows 8..15 are zero padding: free in an HBM-bound kernel).  Fragments
+// are read from shared memory with conflict-free 128-bit loads and NO transposes, because the MMA
+// k-index is permuted to match memory:
+//   S = Q K^T : lane (g,t) reads the 16-byte chunks c = 2t + (j&1) + 8(j>>1), j = 0..3, of token
+//               g's K row and uses them as the B fragments of k-steps 2j, 2j+1; Q's A fragments
+//               are loaded in the same dim order (a dot product does not care).
+//   O = P V   : lane (g,t) reads chunks g and 8+g of V rows 2t, 2t+1, 8+2t, 9+2t — the tokens
+//               whose probabilities it already holds in its S accumulators — and interleaves
+//               them pairwise (PRMT) into B fragments; output column g of n-tile j is head dim
+//               64(j>>3) + 8g + (j&7).
 template <int G>
-__global__ void __launch_bounds__(128, 4)
-decode_attn_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ kv_cache,
+__global__ void __launch_bounds__(kAttnThreads, 3)
+decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat16* __restrict__ q,
                    const int* __restrict__ block_table, int max_blocks,
                    const int* __restrict__ seq_lens, float* __restrict__ scratch_o,
                    float* __restrict__ scratch_ml, int* __restrict__ counters,
                    __nv_bfloat16* __restrict__ out, int n_heads, int n_kv_heads, int max_splits,
                    float scale_log2e) {
-  __shared__ float sm_acc[4][G][128];
+  extern __shared__ uint8_t attn_smem_raw[];
+  uint8_t* ring = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(attn_smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  __shared__ uint64_t full_bar[kAttnStages];
+  __shared__ uint64_t empty_bar[kAttnStages];
+  // per-warp partial outputs reuse the ring once every page has been consumed (keeps the CTA at
+  // 65 KB of shared memory -> 3 CTAs per SM)
+  float (*sm_acc)[G][128] = reinterpret_cast<float (*)[G][128]>(ring);
   __shared__ float sm_m[4][G];
   __shared__ float sm_l[4][G];
   __shared__ int sm_last;
   pdl_launch_dependents();
-  pdl_wait();
+
   const int split = blockIdx.x;
   const int kvh = blockIdx.y;
   const int head0 = kvh * G;
   const int b = blockIdx.z;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int g = lane >> 2, t = lane & 3;
-  // Everything that does not depend on seq_len is requested up front, in parallel: the row's
-  // length, this warp's (at most 4) block-table entries and the query fragments.  Only the K/V
-  // page loads then sit on the critical path, one round trip per page.
-  const int pg0 = split * (kSplitTokens / kPage) + warp;
-  int phys[4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int pg = pg0 + 4 * i;
-    phys[i] = (pg < max_blocks) ? block_table[static_cast<long long>(b) * max_blocks + pg] : 0;
-  }
-  // Q as A fragments: [k-step][a0 (k 2t,2t+1), a2 (k 8+2t,9+2t)]; rows 8..15 (a1, a3) are zero
-  uint32_t qa[8][2];
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    uint4 raw = make_uint4(0u, 0u, 0u, 0u);
-    if (g < G) {
-      raw = *reinterpret_cast<const uint4*>(q + (static_cast<long long>(b) * n_heads + head0 + g) * 128 +
-                                            8 * (t + 4 * j));
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&kv_map);
+    for (int i = 0; i < kAttnStages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
     }
-    qa[2 * j][0] = raw.x; qa[2 * j][1] = raw.y;
-    qa[2 * j + 1][0] = raw.z; qa[2 * j + 1][1] = raw.w;
+    fence_barrier_init();
   }
+  pdl_wait();
   const int seq_len = seq_lens[b];
   const int n_splits = (seq_len + kSplitTokens - 1) / kSplitTokens;
-  if (split < n_splits) {
-    const int tok0 = split * kSplitTokens;
-    const int tok1 = min(seq_len, tok0 + kSplitTokens);
+  if (split >= n_splits) return;  // whole CTA
+  __syncthreads();
+  const int tok0 = split * kSplitTokens;
+  const int tok1 = min(seq_len, tok0 + kSplitTokens);
+  const int n_pages = (tok1 - tok0 + kPage - 1) / kPage;
 
+  if (warp == 4) {
+    // ------------------------------ TMA producer ------------------------------
+    const int my_pg = tok0 / kPage + lane;
+    int my_phys = 0;
+    if (lane < n_pages && my_pg < max_blocks) my_phys = block_table[static_cast<long long>(b) * max_blocks + my_pg];
+    for (int p = 0; p < n_pages; ++p) {
+      const int phys = __shfl_sync(0xffffffffu, my_phys, p);
+      if (lane == 0) {
+        const int stage = p % kAttnStages;
+        if (p >= kAttnStages) mbar_wait(&empty_bar[stage], ((p / kAttnStages) - 1) & 1);
+        uint8_t* dst = ring + stage * kAttnStageBytes;
+        const int row_k = ((phys * 2) * n_kv_heads + kvh) * kPage;
+        const int row_v = ((phys * 2 + 1) * n_kv_heads + kvh) * kPage;
+        mbar_arrive_expect_tx(&full_bar[stage], kAttnStageBytes);
+        tma_load_2d(dst, &kv_map, &full_bar[stage], 0, row_k, kEvictFirst);
+        tma_load_2d(dst + 2048, &kv_map, &full_bar[stage], 64, row_k, kEvictFirst);
+        tma_load_2d(dst + 4096, &kv_map, &full_bar[stage], 0, row_v, kEvictFirst);
+        tma_load_2d(dst + 6144, &kv_map, &full_bar[stage], 64, row_v, kEvictFirst);
+      }
+    }
+  } else {
+    // ------------------------------ consumers ---------------------------------
+    const int g = lane >> 2, t = lane & 3;
+    // Q as A fragments: [k-step][a0 (k 2t,2t+1), a2 (k 8+2t,9+2t)]; rows 8..15 (a1, a3) are zero
+    uint32_t qa[8][2];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      uint4 raw = make_uint4(0u, 0u, 0u, 0u);
+      if (g < G) {
+        const int c = 2 * t + (j & 1) + 8 * (j >> 1);
+        raw = *reinterpret_cast<const uint4*>(q + (static_cast<long long>(b) * n_heads + head0 + g) * 128 + 8 * c);
+      }
+      qa[2 * j][0] = raw.x; qa[2 * j][1] = raw.y;
+      qa[2 * j + 1][0] = raw.z; qa[2 * j + 1][1] = raw.w;
+    }
     float o[16][2];
 #pragma unroll
     for (int j = 0; j < 16; ++j) o[j][0] = o[j][1] = 0.f;
     float m_run = -INFINITY, l_run = 0.f;  // row g (replicated over the quad; l is a quad-partial)
+    const int vt[4] = {2 * t, 2 * t + 1, 8 + 2 * t, 9 + 2 * t};
+    const uint32_t ring_u32 = smem_u32(ring);
 
-#pragma unroll
-    for (int it = 0; it < 4; ++it) {
-      const int pg = pg0 + 4 * it;
-      if (pg * kPage >= tok1) break;
-      const __nv_bfloat16* kbase =
-          kv_cache + ((static_cast<long long>(phys[it]) * 2 * n_kv_heads) + kvh) * (kPage * 128);
-      const __nv_bfloat16* vbase = kbase + static_cast<long long>(n_kv_heads) * (kPage * 128);
-      uint4 kf[2][4], vf[4][2];
-#pragma unroll
-      for (int nt = 0; nt < 2; ++nt)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) kf[nt][j] = ldg_nc_v4(kbase + (nt * 8 + g) * 128 + 8 * (t + 4 * j));
-      const int vt[4] = {2 * t, 2 * t + 1, 8 + 2 * t, 9 + 2 * t};
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        vf[i][0] = ldg_nc_v4(vbase + vt[i] * 128 + 16 * g);
-        vf[i][1] = ldg_nc_v4(vbase + vt[i] * 128 + 16 * g + 8);
-      }
+    for (int p = warp; p < n_pages; p += 4) {
+      const int stage = p % kAttnStages;
+      mbar_wait(&full_bar[stage], (p / kAttnStages) & 1);
+      const uint32_t sk = ring_u32 + stage * kAttnStageBytes;
+      const uint32_t sv = sk + 4096;
       // ---- S = Q K^T
       float s[2][2];
 #pragma unroll
       for (int nt = 0; nt < 2; ++nt) {
         s[nt][0] = s[nt][1] = 0.f;
+        const int row = nt * 8 + g;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          mma_top8(s[nt][0], s[nt][1], qa[2 * j][0], qa[2 * j][1], kf[nt][j].x, kf[nt][j].y);
-          mma_top8(s[nt][0], s[nt][1], qa[2 * j + 1][0], qa[2 * j + 1][1], kf[nt][j].z, kf[nt][j].w);
+          const int cc = 2 * t + (j & 1);  // chunk inside the 64-column box j>>1
+          const uint4 kf = lds_v4(sk + (j >> 1) * 2048 + row * 128 + ((cc ^ (row & 7)) << 4));
+          mma_top8(s[nt][0], s[nt][1], qa[2 * j][0], qa[2 * j][1], kf.x, kf.y);
+          mma_top8(s[nt][0], s[nt][1], qa[2 * j + 1][0], qa[2 * j + 1][1], kf.z, kf.w);
         }
       }
       // ---- online softmax of row g over this page's 16 tokens (this lane: tokens vt[0..3])
-      const int base_tok = pg * kPage;
-      float sv[4];
+      const int base_tok = tok0 + p * kPage;
+      float sv4[4];
       bool ok[4];
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         ok[i] = base_tok + vt[i] < tok1;
-        sv[i] = ok[i] ? s[i >> 1][i & 1] * scale_log2e : -INFINITY;
+        sv4[i] = ok[i] ? s[i >> 1][i & 1] * scale_log2e : -INFINITY;
       }
-      float mx = fmaxf(fmaxf(sv[0], sv[1]), fmaxf(sv[2], sv[3]));
+      float mx = fmaxf(fmaxf(sv4[0], sv4[1]), fmaxf(sv4[2], sv4[3]));
       mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
       mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
       const float m_new = fmaxf(m_run, mx);
       const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
       const float corr = exp2f(m_run - m_use);
       m_run = m_new;
-      float p[4];
+      float pr[4];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) p[i] = exp2f(sv[i] - m_use);
-      l_run = l_run * corr + (p[0] + p[1]) + (p[2] + p[3]);
-      const uint32_t pa0 = pack_bf16(p[0], p[1]);
-      const uint32_t pa2 = pack_bf16(p[2], p[3]);
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        if (!ok[i]) {  // never multiply stale cache contents (possibly non-finite) by p = 0
-          vf[i][0] = make_uint4(0u, 0u, 0u, 0u);
-          vf[i][1] = make_uint4(0u, 0u, 0u, 0u);
-        }
-      }
+      for (int i = 0; i < 4; ++i) pr[i] = exp2f(sv4[i] - m_use);
+      l_run = l_run * corr + (pr[0] + pr[1]) + (pr[2] + pr[3]);
+      const uint32_t pa0 = pack_bf16(pr[0], pr[1]);
+      const uint32_t pa2 = pack_bf16(pr[2], pr[3]);
       // ---- O = O * corr + P V
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        o[j][0] *= corr;
-        o[j][1] *= corr;
-        const int h = j >> 3, w = (j & 7) >> 1;
-        const uint32_t sel = (j & 1) ? 0x7632u : 0x5410u;
-        const uint32_t* v0 = reinterpret_cast<const uint32_t*>(&vf[0][h]);
-        const uint32_t* v1 = reinterpret_cast<const uint32_t*>(&vf[1][h]);
-        const uint32_t* v2 = reinterpret_cast<const uint32_t*>(&vf[2][h]);
-        const uint32_t* v3 = reinterpret_cast<const uint32_t*>(&vf[3][h]);
-        const uint32_t b0 = __byte_perm(v0[w], v1[w], sel);
-        const uint32_t b1 = __byte_perm(v2[w], v3[w], sel);
-        mma_top8(o[j][0], o[j][1], pa0, pa2, b0, b1);
+      for (int h = 0; h < 2; ++h) {
+        uint4 vf[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          vf[i] = lds_v4(sv + h * 2048 + vt[i] * 128 + ((g ^ (vt[i] & 7)) << 4));
+          // never multiply stale cache contents (possibly non-finite) by p = 0
+          if (!ok[i]) vf[i] = make_uint4(0u, 0u, 0u, 0u);
+        }
+#pragma unroll
+        for (int jj = 0; jj < 8; ++jj) {
+          const int j = h * 8 + jj;
+          o[j][0] *= corr;
+          o[j][1] *= corr;
+          const int w = jj >> 1;
+          const uint32_t sel = (jj & 1) ? 0x7632u : 0x5410u;
+          const uint32_t* v0 = reinterpret_cast<const uint32_t*>(&vf[0]);
+          const uint32_t* v1 = reinterpret_cast<const uint32_t*>(&vf[1]);
+          const uint32_t* v2 = reinterpret_cast<const uint32_t*>(&vf[2]);
+          const uint32_t* v3 = reinterpret_cast<const uint32_t*>(&vf[3]);
+          mma_top8(o[j][0], o[j][1], pa0, pa2, __byte_perm(v0[w], v1[w], sel),
+                   __byte_perm(v2[w], v3[w], sel));
+        }
       }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty_bar[stage]);
     }
     l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
     l_run += __shfl_xor_sync(0xffffffffu, l_run, 2);
+    asm volatile("bar.sync 1, 128;" ::: "memory");  // all four consumer warps are done with the ring
     if (g < G) {
 #pragma unroll
       for (int j = 0; j < 16; ++j) {
-        sm_acc[warp][g][16 * (2 * t) + j] = o[j][0];
-        sm_acc[warp][g][16 * (2 * t + 1) + j] = o[j][1];
+        const int dim = 64 * (j >> 3) + (j & 7);
+        sm_acc[warp][g][dim + 8 * (2 * t)] = o[j][0];
+        sm_acc[warp][g][dim + 8 * (2 * t + 1)] = o[j][1];
       }
       if (t == 0) {
         sm_m[warp][g] = m_run;
         sm_l[warp][g] = l_run;
       }
     }
-    __syncthreads();
-    const int tid = threadIdx.x;
+  }
+  __syncthreads();
+  const int tid = threadIdx.x;
+  if (tid < 128) {
 #pragma unroll
     for (int gg = 0; gg < G; ++gg) {
       float mm = fmaxf(fmaxf(sm_m[0][gg], sm_m[1][gg]), fmaxf(sm_m[2][gg], sm_m[3][gg]));
@@ -209,54 +259,54 @@ decode_attn_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __r
         scratch_ml[idx * 2 + 1] = ll;
       }
     }
-    // ---- the chunk that finishes last merges all chunks of this (row, KV head), always in chunk
-    // order, so the result does not depend on which CTA happens to be last
+  }
+  // ---- the chunk that finishes last merges all chunks of this (row, KV head), always in chunk
+  // order, so the result does not depend on which CTA happens to be last
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    const int prev = atomicAdd(&counters[b * n_kv_heads + kvh], 1);
+    sm_last = (prev == n_splits - 1);
+  }
+  __syncthreads();
+  if (sm_last && tid < 128) {
     __threadfence();
-    __syncthreads();
-    if (tid == 0) {
-      const int prev = atomicAdd(&counters[b * n_kv_heads + kvh], 1);
-      sm_last = (prev == n_splits - 1);
-    }
-    __syncthreads();
-    if (sm_last) {
-      __threadfence();
 #pragma unroll
-      for (int gg = 0; gg < G; ++gg) {
-        const long long base = (static_cast<long long>(b) * n_heads + head0 + gg) * max_splits;
-        // loads are issued eight chunks at a time (independent), the arithmetic stays in chunk order
-        float mm = -INFINITY;
-        for (int s0 = 0; s0 < n_splits; s0 += 8) {
-          float mv[8];
+    for (int gg = 0; gg < G; ++gg) {
+      const long long base = (static_cast<long long>(b) * n_heads + head0 + gg) * max_splits;
+      // loads are issued eight chunks at a time (independent), the arithmetic stays in chunk order
+      float mm = -INFINITY;
+      for (int s0 = 0; s0 < n_splits; s0 += 8) {
+        float mv[8];
 #pragma unroll
-          for (int k = 0; k < 8; ++k) mv[k] = (s0 + k < n_splits) ? __ldcg(&scratch_ml[(base + s0 + k) * 2]) : -INFINITY;
+        for (int k = 0; k < 8; ++k) mv[k] = (s0 + k < n_splits) ? __ldcg(&scratch_ml[(base + s0 + k) * 2]) : -INFINITY;
 #pragma unroll
-          for (int k = 0; k < 8; ++k) mm = fmaxf(mm, mv[k]);
-        }
-        const float mu = (mm == -INFINITY) ? 0.f : mm;
-        float oo = 0.f, ll = 0.f;
-        for (int s0 = 0; s0 < n_splits; s0 += 8) {
-          float mv[8], lv[8], ov[8];
-#pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            const bool in = s0 + k < n_splits;
-            mv[k] = in ? __ldcg(&scratch_ml[(base + s0 + k) * 2]) : -INFINITY;
-            lv[k] = in ? __ldcg(&scratch_ml[(base + s0 + k) * 2 + 1]) : 0.f;
-            ov[k] = in ? __ldcg(&scratch_o[(base + s0 + k) * 128 + tid]) : 0.f;
-          }
-#pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            if (s0 + k < n_splits) {
-              const float c = exp2f(mv[k] - mu);
-              oo += ov[k] * c;
-              ll += lv[k] * c;
-            }
-          }
-        }
-        out[(static_cast<long long>(b) * n_heads + head0 + gg) * 128 + tid] =
-            __float2bfloat16_rn(ll > 0.f ? oo / ll : 0.f);
+        for (int k = 0; k < 8; ++k) mm = fmaxf(mm, mv[k]);
       }
-      if (tid == 0) counters[b * n_kv_heads + kvh] = 0;  // leave the counters zero for the next call
+      const float mu = (mm == -INFINITY) ? 0.f : mm;
+      float oo = 0.f, ll = 0.f;
+      for (int s0 = 0; s0 < n_splits; s0 += 8) {
+        float mv[8], lv[8], ov[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const bool in = s0 + k < n_splits;
+          mv[k] = in ? __ldcg(&scratch_ml[(base + s0 + k) * 2]) : -INFINITY;
+          lv[k] = in ? __ldcg(&scratch_ml[(base + s0 + k) * 2 + 1]) : 0.f;
+          ov[k] = in ? __ldcg(&scratch_o[(base + s0 + k) * 128 + tid]) : 0.f;
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          if (s0 + k < n_splits) {
+            const float c = exp2f(mv[k] - mu);
+            oo += ov[k] * c;
+            ll += lv[k] * c;
+          }
+        }
+      }
+      out[(static_cast<long long>(b) * n_heads + head0 + gg) * 128 + tid] =
+          __float2bfloat16_rn(ll > 0.f ? oo / ll : 0.f);
     }
+    if (tid == 0) counters[b * n_kv_heads + kvh] = 0;  // leave the counters zero for the next call
   }
 }
 
@@ -265,13 +315,23 @@ static int launch_decode(const void* q, const void* kv_cache, const int* block_t
                          int max_blocks, const int* seq_lens, float* scratch_o, float* scratch_ml,
                          int* counters, void* out, int B, int n_heads, int n_kv_heads,
                          int max_splits, float scale, cudaStream_t stream) {
+  constexpr int SMEM = kAttnStages * kAttnStageBytes + 1024;
+  static bool configured = false;
+  if (!configured) {
+    BCG_CUDA_CHECK(cudaFuncSetAttribute(decode_attn_kernel<G>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    configured = true;
+  }
+  // The layer's cache as a [token-rows, 128] bf16 tensor; the row count only bounds TMA's
+  // out-of-range check, the block table never points past the real allocation.
+  CUtensorMap kv_map;
+  const int rc = make_tmap_bf16_sw128(&kv_map, kv_cache, 1ll << 30, 128, 128, kPage);
+  if (rc != BCG_OK) return rc;
   dim3 grid(max_splits, n_kv_heads, B);
-  BCG_CUDA_CHECK(launch_k(decode_attn_kernel<G>, grid, dim3(128), 0, stream,
-                          reinterpret_cast<const __nv_bfloat16*>(q),
-                          reinterpret_cast<const __nv_bfloat16*>(kv_cache), block_table, max_blocks,
-                          seq_lens, scratch_o, scratch_ml, counters,
-                          reinterpret_cast<__nv_bfloat16*>(out), n_heads, n_kv_heads, max_splits,
-                          scale * 1.4426950408889634f));
+  BCG_CUDA_CHECK(launch_k(decode_attn_kernel<G>, grid, dim3(kAttnThreads), SMEM, stream, kv_map,
+                          reinterpret_cast<const __nv_bfloat16*>(q), block_table, max_blocks, seq_lens,
+                          scratch_o, scratch_ml, counters, reinterpret_cast<__nv_bfloat16*>(out),
+                          n_heads, n_kv_heads, max_splits, scale * 1.4426950408889634f));
   return BCG_OK;
 }
 

@@ -330,8 +330,8 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // rows x K bf16, row pitch ld elements; box = 64 (K) x box_rows, 128B swizzle, OOB -> 0.
-static int make_tmap(CUtensorMap* m, const void* ptr, long long rows, long long K, long long ld,
-                     int box_rows) {
+int make_tmap_bf16_sw128(CUtensorMap* m, const void* ptr, long long rows, long long K, long long ld,
+                         int box_rows) {
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) {
     set_last_error("cuTensorMapEncodeTiled", "driver entry point unavailable");
@@ -474,11 +474,11 @@ int gemm_bf16_tn(const void* X, const void* W, void* out, int M, int N, int K, l
   CUtensorMap tma, tmb;
   int rc;
   if (swap) {
-    if ((rc = make_tmap(&tma, W, N, K, ldw, kBlockA)) != BCG_OK) return rc;
-    if ((rc = make_tmap(&tmb, X, M, K, ldx, bn)) != BCG_OK) return rc;
+    if ((rc = make_tmap_bf16_sw128(&tma, W, N, K, ldw, kBlockA)) != BCG_OK) return rc;
+    if ((rc = make_tmap_bf16_sw128(&tmb, X, M, K, ldx, bn)) != BCG_OK) return rc;
   } else {
-    if ((rc = make_tmap(&tma, X, M, K, ldx, kBlockA)) != BCG_OK) return rc;
-    if ((rc = make_tmap(&tmb, W, N, K, ldw, bn)) != BCG_OK) return rc;
+    if ((rc = make_tmap_bf16_sw128(&tma, X, M, K, ldx, kBlockA)) != BCG_OK) return rc;
+    if ((rc = make_tmap_bf16_sw128(&tmb, W, N, K, ldw, bn)) != BCG_OK) return rc;
   }
   const int pdl = a.pdl_wait_b;
   switch (bn) {

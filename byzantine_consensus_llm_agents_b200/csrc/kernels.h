@@ -3,6 +3,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <cuda.h>
+
 #include "../../include/bcg_b200.h"
 
 namespace bcg {
@@ -11,6 +13,10 @@ int gemm_bf16_tn(const void* X, const void* W, void* out, int M, int N, int K, l
                  long long ldw, long long ld_out, int epi, int splits, int flags,
                  cudaStream_t stream);
 int gemm_splits_for(int M, int N, int K);
+// TMA descriptor of a row-major bf16 matrix (rows x K, pitch ld elements): boxes of box_rows x 64
+// elements land in shared memory 128B-swizzled, out-of-bounds elements read as zero.
+int make_tmap_bf16_sw128(CUtensorMap* m, const void* ptr, long long rows, long long K, long long ld,
+                         int box_rows);
 
 int embed_rmsnorm(const int* ids, const void* embed, const float* w, float* residual, void* xn,
                   int T, int d, float eps, cudaStream_t stream);
