@@ -95,6 +95,11 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
     return BCG_ERR_TOO_LARGE;
   }
   const int gf = flags & BCG_GEMM_PDL;
+  // profiling aids (tools/step_ablation.py): leave one kernel family out of the step to read its
+  // in-pipeline cost off the step time.  Results are garbage with any of these set.
+  const bool skip_attn = flags & 0x100, skip_norm = flags & 0x200, skip_rope = flags & 0x400;
+  const bool skip_qkv = flags & 0x1000, skip_o = flags & 0x2000, skip_gu = flags & 0x4000,
+             skip_dn = flags & 0x8000, skip_lm = flags & 0x10000;
   struct FlagScope {
     int saved;
     explicit FlagScope(int f) : saved(launch_flags()) { launch_flags() = f; }
@@ -104,24 +109,30 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
   for (int l = 0; l < m->n_layers; ++l) {
     if (l == 0) {
       BCG_TRY(embed_rmsnorm(ids, m->embed, m->ln1[0], ws->residual, ws->xn, B, d, m->rms_eps, st));
-    } else {
+    } else if (!skip_norm) {
       BCG_TRY(add_rmsnorm(ws->residual, P, 1, s_dn, static_cast<long long>(B) * d, m->ln1[l], ws->xn,
                           nullptr, B, d, m->rms_eps, st));
     }
+    if (!skip_qkv)
     BCG_TRY(gemm_bf16_tn(ws->xn, m->w_qkv[l], P, B, qkv_dim, d, d, d, qkv_dim, BCG_EPI_F32, s_qkv, gf,
                          st));
+    if (!skip_rope)
     BCG_TRY(qknorm_rope_kvwrite(P, 1, s_qkv, static_cast<long long>(B) * qkv_dim, qkv_dim,
                                 m->q_norm ? m->q_norm[l] : nullptr,
                                 m->k_norm ? m->k_norm[l] : nullptr, m->cos_sin, positions, slot_map,
                                 ws->q, m->kv_cache[l], B, hq, hkv, m->page_size, m->rms_eps, st));
+    if (!skip_attn)
     BCG_TRY(decode_attn_paged(ws->q, m->kv_cache[l], block_table, max_blocks, seq_lens, ws->attn,
                               ws->attn_scratch_o, ws->attn_scratch_ml, ws->attn_counters, B, hq, hkv,
                               m->page_size, ws->max_splits, scale, st));
+    if (!skip_o)
     BCG_TRY(gemm_bf16_tn(ws->attn, m->w_o[l], P, B, d, hq * 128, hq * 128, hq * 128, d, BCG_EPI_F32,
                          s_o, gf, st));
+    if (!skip_norm)
     BCG_TRY(add_rmsnorm(ws->residual, P, 1, s_o, static_cast<long long>(B) * d, m->ln2[l], ws->xn,
                         nullptr, B, d, m->rms_eps, st));
-    if (s_gu == 1) {
+    if (skip_gu) {
+    } else if (s_gu == 1) {
       BCG_TRY(gemm_bf16_tn(ws->xn, m->w_gate_up[l], ws->act, B, 2 * ff, d, d, d, ff, BCG_EPI_SWIGLU, 1,
                            gf, st));
     } else {
@@ -129,10 +140,12 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
                            gf, st));
       BCG_TRY(swiglu_reduce(P, s_gu, static_cast<long long>(B) * 2 * ff, ws->act, B, 2 * ff, st));
     }
+    if (!skip_dn)
     BCG_TRY(gemm_bf16_tn(ws->act, m->w_down[l], P, B, d, ff, ff, ff, d, BCG_EPI_F32, s_dn, gf, st));
   }
   BCG_TRY(add_rmsnorm(ws->residual, P, 1, s_dn, static_cast<long long>(B) * d, m->final_norm,
                       ws->xn_last, nullptr, B, d, m->rms_eps, st));
+  if (!skip_lm)
   BCG_TRY(gemm_bf16_tn(ws->xn_last, m->lm_head, ws->logits, B, m->vocab, d, d, d, m->vocab,
                        BCG_EPI_F32, 1, gf, st));
   return BCG_OK;
