@@ -196,8 +196,8 @@ def kernel_roofline(engine, B: int, hbm_peak: float, peak_kind: str):
 
 
 # ---- CPU baseline (oracle port) --------------------------------------------------------------
-def cpu_baseline(model_key: str, rounds, n_agents: int, layers_sample: int = 2, decode_steps: int = 8,
-                 prefill_tokens: int = 256):
+def cpu_baseline(model_key: str, rounds, n_agents: int, layers_sample: int = 2, decode_steps: int = 48,
+                 prefill_tokens: int = 1024):
     """Times the CPU oracle (transformers fp32 forward with KV cache; xgrammar + sampler cost is
     included in the decode steps) on a bounded sample and extrapolates to one full agent step:
     a `layers_sample`-layer, full-width model; per-layer and head costs separated; B = 1 per agent
