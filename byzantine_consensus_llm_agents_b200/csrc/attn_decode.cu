@@ -4,8 +4,8 @@
 // row's arithmetic — chunk boundaries and the order partial results are merged in —
 // depends only on that row's own length, never on which other rows share the batch.
 //
-// Phase 1  decode_attn_kernel  grid (max_splits, n_kv_heads, B), 160 threads:
-//          a producer warp streams the chunk's pages through an 8-stage TMA ring, four consumer
+// Phase 1  decode_attn_kernel  grid (max_splits, n_kv_heads, B), 96 threads, 4 CTAs per SM:
+//          a producer warp streams the chunk's pages through a 6-stage TMA ring, two consumer
 //          warps run QK^T and PV on m16n8k16 bf16 MMAs with an fp32 online softmax, partial
 //          (m, l, o[128]) per (row, head, chunk) go to scratch.
 // Phase 2  (same kernel) the chunk CTA that finishes last — found with one atomic counter per
@@ -35,10 +35,15 @@ __device__ __forceinline__ void mma_top8(float& c0, float& c1, uint32_t a0, uint
       : "r"(a0), "r"(a2), "r"(b0), "r"(b1), "r"(0u), "f"(0.f));
 }
 
-constexpr int kAttnStages = 8;                       // ring of {K page, V page} = 8 KB stages
-static_assert(kSplitTokens / kPage <= 2 * kAttnStages, "each ring stage may be used at most twice per chunk (phase parity)");
+constexpr int kAttnStages = 6;                       // ring of {K page, V page} = 8 KB stages
 constexpr int kAttnStageBytes = 2 * kPage * 128 * 2;  // 8192
-constexpr int kAttnThreads = 160;                     // 4 consumer warps + 1 TMA producer warp
+constexpr int kAttnConsumers = 2;                     // consumer warps; + 1 TMA producer warp
+constexpr int kAttnThreads = (kAttnConsumers + 1) * 32;
+// Page p of a chunk lives in stage p % kAttnStages and is consumed by warp p % kAttnConsumers.
+// kAttnStages is a multiple of kAttnConsumers, so every use of a stage is consumed by the SAME
+// warp, in order — which is what makes waiting on a one-bit phase parity safe when a stage is
+// reused more than twice within a chunk.
+static_assert(kAttnStages % kAttnConsumers == 0, "a ring stage must always be consumed by the same warp");
 
 __device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
   uint4 r;
@@ -50,11 +55,11 @@ __device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
 
 // G = q-heads per KV head (1..8).  One CTA = one (row, KV head, 256-token chunk = 16 pages).
 //
-// Data movement: warp 4 is a TMA producer.  The layer's KV cache is described to TMA as one
+// Data movement: the last warp is a TMA producer.  The layer's KV cache is described to TMA as one
 // 2-D bf16 tensor [token-rows, 128]; a page's K (or V) slab is 16 consecutive rows and arrives
 // as two 16 x 64 boxes in the 128B-swizzled layout.  The producer looks up the chunk's block-
-// table entries once and issues every page of the chunk as fast as the 8-stage ring allows, so
-// up to 64 KB per CTA (192 KB per SM at 3 CTAs) is in flight without holding a single register
+// table entries once and issues every page of the chunk as fast as the 6-stage ring allows, so
+// up to 48 KB per CTA (192 KB per SM at 4 CTAs) is in flight without holding a single register
 // — the kernel is bandwidth-bound, not latency-bound.
 //
 // Math: both products run on bf16 tensor-core MMAs (m16n8k16, fp32 accumulate) with the G query
@@ -69,7 +74,7 @@ __device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
 //               them pairwise (PRMT) into B fragments; output column g of n-tile j is head dim
 //               64(j>>3) + 8g + (j&7).
 template <int G>
-__global__ void __launch_bounds__(kAttnThreads, 3)
+__global__ void __launch_bounds__(kAttnThreads, 4)
 decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat16* __restrict__ q,
                    const int* __restrict__ block_table, int max_blocks,
                    const int* __restrict__ seq_lens, float* __restrict__ scratch_o,
@@ -84,8 +89,8 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
   // per-warp partial outputs reuse the ring once every page has been consumed (keeps the CTA at
   // 65 KB of shared memory -> 3 CTAs per SM)
   float (*sm_acc)[G][128] = reinterpret_cast<float (*)[G][128]>(ring);
-  __shared__ float sm_m[4][G];
-  __shared__ float sm_l[4][G];
+  __shared__ float sm_m[kAttnConsumers][G];
+  __shared__ float sm_l[kAttnConsumers][G];
   __shared__ int sm_last;
   pdl_launch_dependents();
 
@@ -111,7 +116,7 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
   const int tok1 = min(seq_len, tok0 + kSplitTokens);
   const int n_pages = (tok1 - tok0 + kPage - 1) / kPage;
 
-  if (warp == 4) {
+  if (warp == kAttnConsumers) {
     // ------------------------------ TMA producer ------------------------------
     const int my_pg = tok0 / kPage + lane;
     int my_phys = 0;
@@ -153,7 +158,7 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
     const int vt[4] = {2 * t, 2 * t + 1, 8 + 2 * t, 9 + 2 * t};
     const uint32_t ring_u32 = smem_u32(ring);
 
-    for (int p = warp; p < n_pages; p += 4) {
+    for (int p = warp; p < n_pages; p += kAttnConsumers) {
       const int stage = p % kAttnStages;
       mbar_wait(&full_bar[stage], (p / kAttnStages) & 1);
       const uint32_t sk = ring_u32 + stage * kAttnStageBytes;
@@ -224,7 +229,7 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
     }
     l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
     l_run += __shfl_xor_sync(0xffffffffu, l_run, 2);
-    asm volatile("bar.sync 1, 128;" ::: "memory");  // all four consumer warps are done with the ring
+    asm volatile("bar.sync 1, %0;" ::"n"(kAttnConsumers * 32) : "memory");  // consumers are done with the ring
     if (g < G) {
 #pragma unroll
       for (int j = 0; j < 16; ++j) {
@@ -240,21 +245,23 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
   }
   __syncthreads();
   const int tid = threadIdx.x;
-  if (tid < 128) {
+  for (int d = tid; d < 128; d += kAttnThreads) {
 #pragma unroll
     for (int gg = 0; gg < G; ++gg) {
-      float mm = fmaxf(fmaxf(sm_m[0][gg], sm_m[1][gg]), fmaxf(sm_m[2][gg], sm_m[3][gg]));
+      float mm = -INFINITY;
+#pragma unroll
+      for (int w = 0; w < kAttnConsumers; ++w) mm = fmaxf(mm, sm_m[w][gg]);
       const float mu = (mm == -INFINITY) ? 0.f : mm;
       float oo = 0.f, ll = 0.f;
 #pragma unroll
-      for (int w = 0; w < 4; ++w) {
-        const float c = exp2f(sm_m[w][gg] - mu);
-        oo += sm_acc[w][gg][tid] * c;
+      for (int w = 0; w < kAttnConsumers; ++w) {
+        const float c = exp2f(sm_m[w][gg] - mu);  // a warp without pages has m = -inf -> weight 0
+        oo += sm_acc[w][gg][d] * c;
         ll += sm_l[w][gg] * c;
       }
       const long long idx = (static_cast<long long>(b) * n_heads + head0 + gg) * max_splits + split;
-      scratch_o[idx * 128 + tid] = oo;
-      if (tid == 0) {
+      scratch_o[idx * 128 + d] = oo;
+      if (d == 0) {
         scratch_ml[idx * 2] = mm;
         scratch_ml[idx * 2 + 1] = ll;
       }
@@ -269,8 +276,9 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
     sm_last = (prev == n_splits - 1);
   }
   __syncthreads();
-  if (sm_last && tid < 128) {
+  if (sm_last) {
     __threadfence();
+    for (int d = tid; d < 128; d += kAttnThreads)
 #pragma unroll
     for (int gg = 0; gg < G; ++gg) {
       const long long base = (static_cast<long long>(b) * n_heads + head0 + gg) * max_splits;
@@ -292,7 +300,7 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
           const bool in = s0 + k < n_splits;
           mv[k] = in ? __ldcg(&scratch_ml[(base + s0 + k) * 2]) : -INFINITY;
           lv[k] = in ? __ldcg(&scratch_ml[(base + s0 + k) * 2 + 1]) : 0.f;
-          ov[k] = in ? __ldcg(&scratch_o[(base + s0 + k) * 128 + tid]) : 0.f;
+          ov[k] = in ? __ldcg(&scratch_o[(base + s0 + k) * 128 + d]) : 0.f;
         }
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
@@ -303,7 +311,7 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
           }
         }
       }
-      out[(static_cast<long long>(b) * n_heads + head0 + gg) * 128 + tid] =
+      out[(static_cast<long long>(b) * n_heads + head0 + gg) * 128 + d] =
           __float2bfloat16_rn(ll > 0.f ? oo / ll : 0.f);
     }
     if (tid == 0) counters[b * n_kv_heads + kvh] = 0;  // leave the counters zero for the next call
