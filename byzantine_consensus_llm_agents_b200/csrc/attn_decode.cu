@@ -108,6 +108,29 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
     fence_barrier_init();
   }
   pdl_wait();
+  // Requests that do not depend on the row's length go out together with the length itself:
+  // the producer's block-table entries (entries past the row's last page are unused) and the
+  // consumers' query fragments.  One memory round trip instead of two before the first TMA.
+  const int g = lane >> 2, t = lane & 3;
+  int my_phys = 0;
+  uint32_t qa[8][2];
+  if (warp == kAttnConsumers) {
+    const int my_pg = split * (kSplitTokens / kPage) + lane;
+    if (lane < kSplitTokens / kPage && my_pg < max_blocks)
+      my_phys = block_table[static_cast<long long>(b) * max_blocks + my_pg];
+  } else {
+    // Q as A fragments: [k-step][a0 (k 2t,2t+1), a2 (k 8+2t,9+2t)]; rows 8..15 (a1, a3) are zero
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      uint4 raw = make_uint4(0u, 0u, 0u, 0u);
+      if (g < G) {
+        const int c = 2 * t + (j & 1) + 8 * (j >> 1);
+        raw = *reinterpret_cast<const uint4*>(q + (static_cast<long long>(b) * n_heads + head0 + g) * 128 + 8 * c);
+      }
+      qa[2 * j][0] = raw.x; qa[2 * j][1] = raw.y;
+      qa[2 * j + 1][0] = raw.z; qa[2 * j + 1][1] = raw.w;
+    }
+  }
   const int seq_len = seq_lens[b];
   const int n_splits = (seq_len + kSplitTokens - 1) / kSplitTokens;
   if (split >= n_splits) return;  // whole CTA
@@ -118,9 +141,6 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
 
   if (warp == kAttnConsumers) {
     // ------------------------------ TMA producer ------------------------------
-    const int my_pg = tok0 / kPage + lane;
-    int my_phys = 0;
-    if (lane < n_pages && my_pg < max_blocks) my_phys = block_table[static_cast<long long>(b) * max_blocks + my_pg];
     for (int p = 0; p < n_pages; ++p) {
       const int phys = __shfl_sync(0xffffffffu, my_phys, p);
       if (lane == 0) {
@@ -138,19 +158,6 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
     }
   } else {
     // ------------------------------ consumers ---------------------------------
-    const int g = lane >> 2, t = lane & 3;
-    // Q as A fragments: [k-step][a0 (k 2t,2t+1), a2 (k 8+2t,9+2t)]; rows 8..15 (a1, a3) are zero
-    uint32_t qa[8][2];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      uint4 raw = make_uint4(0u, 0u, 0u, 0u);
-      if (g < G) {
-        const int c = 2 * t + (j & 1) + 8 * (j >> 1);
-        raw = *reinterpret_cast<const uint4*>(q + (static_cast<long long>(b) * n_heads + head0 + g) * 128 + 8 * c);
-      }
-      qa[2 * j][0] = raw.x; qa[2 * j][1] = raw.y;
-      qa[2 * j + 1][0] = raw.z; qa[2 * j + 1][1] = raw.w;
-    }
     float o[16][2];
 #pragma unroll
     for (int j = 0; j < 16; ++j) o[j][0] = o[j][1] = 0.f;
