@@ -41,7 +41,7 @@ ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
 HF_NAME = {"qwen3-14b": "Qwen/Qwen3-14B", "qwen3-8b": "Qwen/Qwen3-8B", "qwen3-0.6b": "Qwen/Qwen3-0.6B",
-           "qwen3-32b": "Qwen/Qwen3-32B"}
+           "qwen3-32b": "Qwen/Qwen3-32B", "mistral-22b": "mistralai/Mistral-Small-Instruct-2409"}
 LLM = {"temperature_decide": 0.5, "temperature_vote": 0.3, "max_tokens_decide": 300,
        "max_tokens_vote": 200}          # reference config.py:52-58
 MAX_RETRIES = 3                          # main.py:269, 386
@@ -56,8 +56,8 @@ def load_peaks():
     return 6650.0, 1590.0, "fallback"
 
 
-def load_rounds(honest: int, byz: int):
-    p = ROOT / "tests" / "golden" / f"bench_prompts_qwen3_{honest}h{byz}b.json.gz"
+def load_rounds(honest: int, byz: int, family: str = "qwen3"):
+    p = ROOT / "tests" / "golden" / f"bench_prompts_{family}_{honest}h{byz}b.json.gz"
     with gzip.open(p, "rt") as f:
         return json.load(f)["rounds"]
 
@@ -215,7 +215,10 @@ def cpu_baseline(model_key: str, rounds, n_agents: int, layers_sample: int = 2, 
     hf = build_hf_model(cfg, seed=0)
     eng = OracleEngine(hf, tk, base_seed=0, memoise=False)
     s, u, schema = rounds[0]["decide"]["prompts"][0]
-    prompt = f"<|im_start|>system\n{s}<|im_end|>\n<|im_start|>user\n{u} /no_think<|im_end|>\n<|im_start|>assistant\n"
+    if full.family == "mistral":
+        prompt = f"<s>[INST] <<SYS>>\n{s}\n<</SYS>>\n\n{u} [/INST]"
+    else:
+        prompt = f"<|im_start|>system\n{s}<|im_end|>\n<|im_start|>user\n{u} /no_think<|im_end|>\n<|im_start|>assistant\n"
     ids = tk.encode(prompt)
     n_prompt = len(ids)
     # (1) prefill sample through the real oracle path
@@ -269,7 +272,7 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
     n_agents = a.honest + a.byzantine
-    rounds = load_rounds(a.honest, a.byzantine)
+    rounds = load_rounds(a.honest, a.byzantine, "mistral" if a.model.startswith("mistral") else "qwen3")
     hbm_peak, tf_peak, peak_kind = load_peaks()
     config = {"workload": f"{a.model} bf16 random-init, {a.honest} honest + {a.byzantine} Byzantine agents, "
                           "one game round per step (decide T=0.5/300 tok + vote T=0.3/200 tok, reference "
