@@ -27,6 +27,7 @@ SOURCES = [
     "attn_prefill.cu",
     "sampler.cu",
     "model_step.cu",
+    "tp_comm.cu",
 ]
 
 NVCC_FLAGS = [
@@ -75,7 +76,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
 
     with ThreadPoolExecutor(max_workers=min(8, len(SOURCES))) as ex:
         objs = list(ex.map(compile_one, SOURCES))
-    cmd = [nvcc, "-shared", "-cudart", "static", "-o", str(LIB), *map(str, objs)]
+    cmd = [nvcc, "-shared", "-cudart", "static", "-o", str(LIB), *map(str, objs), "-ldl"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)

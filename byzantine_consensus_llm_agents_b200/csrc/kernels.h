@@ -46,4 +46,13 @@ int prefill_attn_paged(const void* q, const void* kv_cache, const int* block_tab
 
 int mask_sample(const bcg_sampler_args* a, cudaStream_t stream);
 
+// tensor parallelism (tp_comm.cu)
+int tp_unique_id(void* out128);
+int tp_init(const void* id128, int rank, int size);
+int tp_shutdown();
+int tp_size();
+int tp_rank();
+int tp_all_reduce_f32(float* buf, long long count, cudaStream_t stream);
+int tp_all_gather_f32(const float* send, float* recv, long long count, cudaStream_t stream);
+
 }  // namespace bcg

@@ -36,6 +36,11 @@ int model_prefill(const bcg_model* m, const bcg_workspace* ws, const int* ids, c
   const int d = m->d_model, hq = m->n_heads, hkv = m->n_kv_heads;
   const int qkv_dim = (hq + 2 * hkv) * 128;
   const float scale = 0.08838834764831845f;  // 1/sqrt(128)
+  const int tp = m->tp_size > 1 ? m->tp_size : 1;
+  if (tp > 1 && (tp_size() != tp || !ws->logits_local)) {
+    set_last_error("bcg_model_prefill", "tp_size does not match bcg_tp_init, or logits_local missing");
+    return BCG_ERR_ARG;
+  }
   for (int l = 0; l < m->n_layers; ++l) {
     if (l == 0) {
       BCG_TRY(embed_rmsnorm(ids, m->embed, m->ln1[0], ws->residual, ws->xn, T, d, m->rms_eps, st));
@@ -53,17 +58,26 @@ int model_prefill(const bcg_model* m, const bcg_workspace* ws, const int* ids, c
                                ws->attn, hq, hkv, m->page_size, scale, st));
     BCG_TRY(gemm_bf16_tn(ws->attn, m->w_o[l], ws->delta, T, d, hq * 128, hq * 128, hq * 128, d,
                          BCG_EPI_F32, 1, 0, st));
+    if (tp > 1) BCG_TRY(tp_all_reduce_f32(ws->delta, static_cast<long long>(T) * d, st));
     BCG_TRY(add_rmsnorm(ws->residual, ws->delta, 1, 1, 0, m->ln2[l], ws->xn, nullptr, T, d,
                         m->rms_eps, st));
     BCG_TRY(gemm_bf16_tn(ws->xn, m->w_gate_up[l], ws->act, T, 2 * m->d_ff, d, d, d, m->d_ff,
                          BCG_EPI_SWIGLU, 1, 0, st));
     BCG_TRY(gemm_bf16_tn(ws->act, m->w_down[l], ws->delta, T, d, m->d_ff, m->d_ff, m->d_ff, d,
                          BCG_EPI_F32, 1, 0, st));
+    if (tp > 1) BCG_TRY(tp_all_reduce_f32(ws->delta, static_cast<long long>(T) * d, st));
   }
   BCG_TRY(add_rmsnorm(ws->residual, ws->delta, 1, 1, 0, m->final_norm, ws->xn_last, last_rows,
                       n_seqs, d, m->rms_eps, st));
-  BCG_TRY(gemm_bf16_tn(ws->xn_last, m->lm_head, ws->logits, n_seqs, m->vocab, d, d, d, m->vocab,
-                       BCG_EPI_F32, 1, 0, st));
+  if (tp > 1) {
+    // vocab-parallel head: local [n_seqs, V/tp] logits, all-gathered rank-major
+    BCG_TRY(gemm_bf16_tn(ws->xn_last, m->lm_head, ws->logits_local, n_seqs, m->vocab, d, d, d, m->vocab,
+                         BCG_EPI_F32, 1, 0, st));
+    BCG_TRY(tp_all_gather_f32(ws->logits_local, ws->logits, static_cast<long long>(n_seqs) * m->vocab, st));
+  } else {
+    BCG_TRY(gemm_bf16_tn(ws->xn_last, m->lm_head, ws->logits, n_seqs, m->vocab, d, d, d, m->vocab,
+                         BCG_EPI_F32, 1, 0, st));
+  }
   return BCG_OK;
 }
 
@@ -93,6 +107,11 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
   if (need > ws->partials_floats) {
     set_last_error("bcg_model_decode", "split-K scratch too small");
     return BCG_ERR_TOO_LARGE;
+  }
+  const int tp = m->tp_size > 1 ? m->tp_size : 1;
+  if (tp > 1 && (tp_size() != tp || !ws->logits_local)) {
+    set_last_error("bcg_model_decode", "tp_size does not match bcg_tp_init, or logits_local missing");
+    return BCG_ERR_ARG;
   }
   const int gf = flags & BCG_GEMM_PDL;
   // profiling aids (tools/step_ablation.py): leave one kernel family out of the step to read its
@@ -128,6 +147,9 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
     if (!skip_o)
     BCG_TRY(gemm_bf16_tn(ws->attn, m->w_o[l], P, B, d, hq * 128, hq * 128, hq * 128, d, BCG_EPI_F32,
                          s_o, gf, st));
+    // row-parallel projection: sum the split-K slabs over the ranks in place (slab s of every rank
+    // adds up to slab s); the norm kernel then adds the slabs as usual
+    if (tp > 1) BCG_TRY(tp_all_reduce_f32(P, static_cast<long long>(s_o) * B * d, st));
     if (!skip_norm)
     BCG_TRY(add_rmsnorm(ws->residual, P, 1, s_o, static_cast<long long>(B) * d, m->ln2[l], ws->xn,
                         nullptr, B, d, m->rms_eps, st));
@@ -142,12 +164,18 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
     }
     if (!skip_dn)
     BCG_TRY(gemm_bf16_tn(ws->act, m->w_down[l], P, B, d, ff, ff, ff, d, BCG_EPI_F32, s_dn, gf, st));
+    if (tp > 1) BCG_TRY(tp_all_reduce_f32(P, static_cast<long long>(s_dn) * B * d, st));
   }
   BCG_TRY(add_rmsnorm(ws->residual, P, 1, s_dn, static_cast<long long>(B) * d, m->final_norm,
                       ws->xn_last, nullptr, B, d, m->rms_eps, st));
-  if (!skip_lm)
-  BCG_TRY(gemm_bf16_tn(ws->xn_last, m->lm_head, ws->logits, B, m->vocab, d, d, d, m->vocab,
-                       BCG_EPI_F32, 1, gf, st));
+  if (tp > 1) {
+    BCG_TRY(gemm_bf16_tn(ws->xn_last, m->lm_head, ws->logits_local, B, m->vocab, d, d, d, m->vocab,
+                         BCG_EPI_F32, 1, gf, st));
+    BCG_TRY(tp_all_gather_f32(ws->logits_local, ws->logits, static_cast<long long>(B) * m->vocab, st));
+  } else if (!skip_lm) {
+    BCG_TRY(gemm_bf16_tn(ws->xn_last, m->lm_head, ws->logits, B, m->vocab, d, d, d, m->vocab,
+                         BCG_EPI_F32, 1, gf, st));
+  }
   return BCG_OK;
 }
 

@@ -103,13 +103,14 @@ mask_sample_kernel(const SamplerDev p) {
     const bool greedy = temp < 1e-5f;
     const uint32_t k0 = a.seed[2 * row], k1 = a.seed[2 * row + 1];
     const uint32_t step = static_cast<uint32_t>(a.n_out[row]);
-    const float* lg = a.logits + static_cast<long long>(row) * a.ld_logits;
+    const float* lg = a.logits + static_cast<long long>(row) * (a.shard_v > 0 ? a.shard_v : a.ld_logits);
     // slice in units of 128 elements so float4 chunks and 32-bit mask words never straddle
     const int per = ((a.V + kSampCluster * 128 - 1) / (kSampCluster * 128)) * 128;
     const int i0 = static_cast<int>(rank) * per;
     const int i1 = min(a.V, i0 + per);
     for (int i = i0 + 4 * threadIdx.x; i < i1; i += 4 * kSampThreads) {
-      const float4 x = *reinterpret_cast<const float4*>(lg + i);
+      const float4 x = *reinterpret_cast<const float4*>(
+          a.shard_v > 0 ? lg + static_cast<long long>(i / a.shard_v) * a.shard_stride + i % a.shard_v : lg + i);
       uint32_t bits = 0xFu;
       if (mask) bits = (static_cast<uint32_t>(mask[i >> 5]) >> (i & 31)) & 0xFu;
       if (bits == 0) continue;
@@ -214,7 +215,7 @@ int mask_sample(const bcg_sampler_args* a, cudaStream_t stream) {
       !a->grammar_id || !a->temperature || !a->seed || !a->max_tokens || !a->state || !a->n_out ||
       !a->finished || !a->out_tokens || !a->next_ids || !a->positions || !a->seq_lens ||
       !a->slot_map || !a->block_table || !a->tok_offsets || !a->tok_bytes || a->page_size <= 0 ||
-      a->mask_words < (a->V + 31) / 32) {
+      a->mask_words < (a->V + 31) / 32 || (a->shard_v > 0 && (a->shard_v % 4))) {
     set_last_error("bcg_mask_sample", "bad argument (null pointer, V % 4, or mask_words too small)");
     return BCG_ERR_ARG;
   }

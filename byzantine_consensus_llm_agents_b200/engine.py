@@ -145,11 +145,20 @@ class Engine:
     def __init__(self, cfg: ModelConfig, weights: Weights, tokenizer, *, max_model_len: int = 8192,
                  max_rows: int = 64, prefill_tokens: int = 16384, kv_pages: Optional[int] = None,
                  gpu_memory_utilization: float = 0.9, base_seed: int = 0, device: str = "cuda:0",
-                 enable_prefix_cache: bool = True, use_cuda_graph: bool = True, pdl: bool = False):
+                 enable_prefix_cache: bool = True, use_cuda_graph: bool = True, pdl: bool = False,
+                 tp_rank: int = 0, tp_size: int = 1):
+        """`cfg` is the FULL architecture; with tp_size > 1 `weights` must be this rank's shard
+        (Weights.shard / random_init_sharded) and bcg_tp_init must have been called (collective)."""
         if not torch.cuda.is_available():
             raise L.BcgError("the engine needs a CUDA device (sm_100a); there is no CPU fallback")
         self.lib = L.load()
         self.cfg, self.w, self.tk = cfg, weights, tokenizer
+        self.tp_rank, self.tp_size = tp_rank, tp_size
+        full_cfg = cfg
+        lcfg = cfg.shard(tp_size)          # this rank's heads / d_ff / vocab
+        self.lcfg = lcfg
+        if tp_size > 1 and weights.cfg.n_heads != lcfg.n_heads:
+            raise L.BcgError("tensor-parallel engine needs sharded weights (Weights.shard)")
         self.dev = torch.device(device)
         torch.cuda.set_device(self.dev)
         self.max_model_len = min(max_model_len, cfg.max_pos)
@@ -168,17 +177,21 @@ class Engine:
         z = lambda *s, dt=bf: torch.zeros(*s, dtype=dt, device=self.dev)
         # ---- workspace (include/bcg_b200.h bcg_workspace)
         self.max_splits_cap = (self.max_model_len + SPLIT_TOKENS - 1) // SPLIT_TOKENS
-        splits = [L.splits_for(1, n, k) for n, k in ((cfg.qkv_dim, d), (d, cfg.n_heads * 128),
-                                                      (2 * cfg.d_ff, d), (d, cfg.d_ff))]
-        pf = max(splits[0] * B * cfg.qkv_dim, splits[1] * B * d,
-                 (splits[2] * B * 2 * cfg.d_ff) if splits[2] > 1 else 0, splits[3] * B * d)
+        lc = lcfg
+        splits = [L.splits_for(1, n, k) for n, k in ((lc.qkv_dim, d), (d, lc.n_heads * 128),
+                                                      (2 * lc.d_ff, d), (d, lc.d_ff))]
+        pf = max(splits[0] * B * lc.qkv_dim, splits[1] * B * d,
+                 (splits[2] * B * 2 * lc.d_ff) if splits[2] > 1 else 0, splits[3] * B * d)
         self.buf = dict(
-            residual=z(T, d, dt=f32), xn=z(T, d), qkv=z(T, cfg.qkv_dim, dt=f32), q=z(T, cfg.n_heads * 128),
-            attn=z(T, cfg.n_heads * 128), act=z(T, cfg.d_ff), delta=z(T, d, dt=f32), partials=z(pf, dt=f32),
-            so=z(B * cfg.n_heads * self.max_splits_cap * 128, dt=f32),
-            sml=z(B * cfg.n_heads * self.max_splits_cap * 2, dt=f32),
-            attn_counters=z(B * cfg.n_kv_heads, dt=i32),
-            logits=z(B, cfg.vocab, dt=f32), xn_last=z(B, d))
+            residual=z(T, d, dt=f32), xn=z(T, d), qkv=z(T, lc.qkv_dim, dt=f32), q=z(T, lc.n_heads * 128),
+            attn=z(T, lc.n_heads * 128), act=z(T, lc.d_ff), delta=z(T, d, dt=f32), partials=z(pf, dt=f32),
+            so=z(B * lc.n_heads * self.max_splits_cap * 128, dt=f32),
+            sml=z(B * lc.n_heads * self.max_splits_cap * 2, dt=f32),
+            attn_counters=z(B * lc.n_kv_heads, dt=i32),
+            logits=z(B, full_cfg.vocab, dt=f32), xn_last=z(B, d))
+        if tp_size > 1:
+            self.buf["logits_local"] = z(B, lc.vocab, dt=f32)
+            self.buf["logits_group"] = z(B, full_cfg.vocab, dt=f32)
         ws = L.Workspace()
         b = self.buf
         ws.residual, ws.xn, ws.qkv, ws.q = b["residual"].data_ptr(), b["xn"].data_ptr(), b["qkv"].data_ptr(), b["q"].data_ptr()
@@ -188,17 +201,18 @@ class Engine:
         ws.attn_counters = b["attn_counters"].data_ptr()
         ws.max_splits = self.max_splits_cap
         ws.logits, ws.xn_last, ws.T_max, ws.B_max = b["logits"].data_ptr(), b["xn_last"].data_ptr(), T, B
+        ws.logits_local = b["logits_local"].data_ptr() if tp_size > 1 else None
         self.ws = ws
         # ---- KV pages
-        page_bytes = 2 * cfg.n_kv_heads * PAGE * 128 * 2 * cfg.n_layers
+        page_bytes = 2 * lc.n_kv_heads * PAGE * 128 * 2 * cfg.n_layers
         if kv_pages is None:
             free_b, total_b = torch.cuda.mem_get_info(self.dev)
             budget = int(total_b * gpu_memory_utilization) - (total_b - free_b)
             want = self.max_rows * self.max_blocks * 2
             kv_pages = max(self.max_blocks + 8, min(want, budget // page_bytes))
-        self.kv_layers = [z(kv_pages, 2, cfg.n_kv_heads, PAGE, 128) for _ in range(cfg.n_layers)]
+        self.kv_layers = [z(kv_pages, 2, lc.n_kv_heads, PAGE, 128) for _ in range(cfg.n_layers)]
         self.pool = PagePool(kv_pages)
-        self.model = ModelHandle(weights, self.kv_layers, PAGE)
+        self.model = ModelHandle(weights, self.kv_layers, PAGE, tp_size)
         # ---- per-row device state (bcg_sampler_args)
         self.row = dict(
             grammar_id=z(B, dt=i32), state=z(B, dt=i32), temperature=z(B, dt=f32), seed=z(B, 2, dt=i32),
@@ -269,6 +283,8 @@ class Engine:
         a.next_ids, a.positions = r["next_ids"].data_ptr(), r["positions"].data_ptr()
         a.seq_lens, a.slot_map = r["seq_lens"].data_ptr(), r["slot_map"].data_ptr()
         a.block_table, a.n_active = r["block_table"].data_ptr(), r["n_active"].data_ptr()
+        if self.tp_size > 1:   # logits as the all-gather left them: [tp][B][V/tp]
+            a.shard_v, a.shard_stride = self.lcfg.vocab, B * self.lcfg.vocab
         return a
 
     def _sample(self, B: int, use_forced: bool) -> None:
@@ -410,7 +426,7 @@ class Engine:
                 for j, h in enumerate(hashes_of[b]):
                     self.pool.publish(pages_of[b][j], h)
         if self.debug_logits is not None:
-            self.debug_logits.append(self.buf["logits"][:B].clone())
+            self.debug_logits.append(self._logits_rows(B))
         self._sample(B, use_forced)          # first token of every row
         self.stats["gpu_launches"] += 2
         ev1.record()
@@ -444,7 +460,7 @@ class Engine:
                     else:
                         self._decode_step(B, max_splits, use_forced)
                         if self.debug_logits is not None:
-                            self.debug_logits.append(self.buf["logits"][:B].clone())
+                            self.debug_logits.append(self._logits_rows(B))
                 steps += n
                 self.stats["gpu_launches"] += n * per_step
                 self.n_active_host.copy_(r["n_active"], non_blocking=True)
@@ -479,6 +495,13 @@ class Engine:
         st["host_s"] += time.perf_counter() - t_host1
         return results
 
+    def _logits_rows(self, B: int) -> torch.Tensor:
+        """[B, V] logits of the current step (un-shards the all-gather layout under TP)."""
+        if self.tp_size == 1:
+            return self.buf["logits"][:B].clone()
+        P, vp = self.tp_size, self.lcfg.vocab
+        return self.buf["logits"].view(-1)[:P * B * vp].view(P, B, vp).permute(1, 0, 2).reshape(B, P * vp).clone()
+
     def _prefill_group(self, b0, b1, ids_list, cached, bt) -> None:
         cfg, dev = self.cfg, self.dev
         ids, pos, slots, tiles, last = [], [], [], [], []
@@ -500,7 +523,11 @@ class Engine:
         self.stats["h2d_bytes"] += sum(x.numel() * 4 for x in (d_ids, d_pos, d_slots, d_tiles, d_last, d_bt))
         # this group's last-token logits go straight to rows b0..b1 of the row-indexed buffer
         base = self.buf["logits"].data_ptr()
-        self.ws.logits = base + b0 * cfg.vocab * 4
+        B_all = len(ids_list)
+        if self.tp_size > 1:
+            self.ws.logits = self.buf["logits_group"].data_ptr()   # gathered [tp][n_seqs][V/tp]
+        else:
+            self.ws.logits = base + b0 * cfg.vocab * 4
         try:
             L.check(self.lib.bcg_model_prefill(C.byref(self.model.struct), C.byref(self.ws),
                                                d_ids.data_ptr(), d_pos.data_ptr(), d_slots.data_ptr(),
@@ -509,6 +536,10 @@ class Engine:
                     "bcg_model_prefill")
         finally:
             self.ws.logits = base
+        if self.tp_size > 1:   # place the group's rows into the call-wide [tp][B][V/tp] layout
+            P, vp = self.tp_size, self.lcfg.vocab
+            dst = self.buf["logits"].view(-1)[:P * B_all * vp].view(P, B_all, vp)
+            dst[:, b0:b1] = self.buf["logits_group"].view(-1)[:P * n_seqs * vp].view(P, n_seqs, vp)
         self.stats["gpu_launches"] += cfg.n_layers * 8 + 2
         self._keepalive = (d_ids, d_pos, d_slots, d_tiles, d_last, d_bt)
 

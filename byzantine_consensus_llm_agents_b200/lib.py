@@ -36,6 +36,7 @@ class SamplerArgs(C.Structure):
         ("state", vp), ("n_out", vp), ("finished", vp), ("out_tokens", vp), ("chosen", vp),
         ("next_ids", vp), ("positions", vp), ("seq_lens", vp), ("slot_map", vp),
         ("block_table", vp), ("n_active", vp),
+        ("shard_v", C.c_int), ("shard_stride", C.c_longlong),
     ]
 
 
@@ -49,7 +50,7 @@ class Model(C.Structure):
         ("w_qkv", C.POINTER(vp)), ("w_o", C.POINTER(vp)),
         ("w_gate_up", C.POINTER(vp)), ("w_down", C.POINTER(vp)),
         ("q_norm", C.POINTER(vp)), ("k_norm", C.POINTER(vp)),
-        ("kv_cache", C.POINTER(vp)), ("cos_sin", vp),
+        ("kv_cache", C.POINTER(vp)), ("cos_sin", vp), ("tp_size", C.c_int),
     ]
 
 
@@ -59,7 +60,7 @@ class Workspace(C.Structure):
         ("delta", vp), ("partials", vp), ("partials_floats", C.c_longlong),
         ("attn_scratch_o", vp), ("attn_scratch_ml", vp), ("attn_counters", vp),
         ("max_splits", C.c_int),
-        ("logits", vp), ("xn_last", vp), ("T_max", C.c_int), ("B_max", C.c_int),
+        ("logits", vp), ("logits_local", vp), ("xn_last", vp), ("T_max", C.c_int), ("B_max", C.c_int),
     ]
 
 
@@ -83,6 +84,9 @@ _SIGS = {
     "bcg_prefill_attn_paged": (C.c_int, [vp, vp, vp, C.c_int, vp, C.c_int, vp, C.c_int, C.c_int,
                                          C.c_int, C.c_float, vp]),
     "bcg_mask_sample": (C.c_int, [C.POINTER(SamplerArgs), vp]),
+    "bcg_tp_unique_id": (C.c_int, [vp]),
+    "bcg_tp_init": (C.c_int, [vp, C.c_int, C.c_int]),
+    "bcg_tp_shutdown": (C.c_int, []),
     "bcg_model_prefill": (C.c_int, [C.POINTER(Model), C.POINTER(Workspace), vp, vp, vp, vp, C.c_int,
                                     vp, C.c_int, vp, C.c_int, C.c_int, vp]),
     "bcg_model_decode": (C.c_int, [C.POINTER(Model), C.POINTER(Workspace), vp, vp, vp, vp, vp,

@@ -41,6 +41,19 @@ class ModelConfig:
     def kv_bytes_per_token(self) -> int:
         return 2 * self.n_layers * self.n_kv_heads * self.head_dim * 2
 
+    def shard(self, tp_size: int) -> "ModelConfig":
+        """This rank's view under tensor parallelism: heads, d_ff and vocabulary divided."""
+        if tp_size == 1:
+            return self
+        for what, n in (("n_heads", self.n_heads), ("n_kv_heads", self.n_kv_heads), ("vocab", self.vocab)):
+            if n % tp_size:
+                raise ValueError(f"{what}={n} is not divisible by tensor_parallel_size={tp_size}")
+        if (self.d_ff // 16) % tp_size:
+            raise ValueError(f"d_ff={self.d_ff} cannot be split {tp_size} ways in 16-row blocks")
+        return ModelConfig(**{**self.__dict__, "n_heads": self.n_heads // tp_size,
+                              "n_kv_heads": self.n_kv_heads // tp_size, "d_ff": self.d_ff // tp_size,
+                              "vocab": self.vocab // tp_size, "name": f"{self.name}/tp{tp_size}"})
+
     def layer_weight_bytes(self) -> int:
         d, f = self.d_model, self.d_ff
         per = self.qkv_dim * d + d * self.n_heads * self.head_dim + 2 * f * d + d * f
@@ -142,6 +155,66 @@ class Weights:
         w.cos_sin = rope_table(cfg, device)
         return w
 
+    def shard(self, rank: int, size: int) -> "Weights":
+        """Column-parallel qkv / gate_up, row-parallel o / down, vocab-parallel lm_head; norms, the
+        embedding and the RoPE table are replicated (what vLLM does for the reference when
+        tensor_parallel_size > 1).  Returns contiguous copies of this rank's slices."""
+        if size == 1:
+            return self
+        c, lc = self.cfg, self.cfg.shard(size)
+        hq, hkv, f, hd = lc.n_heads, lc.n_kv_heads, lc.d_ff, c.head_dim
+        qo, ko, vo = 0, c.n_heads * hd, (c.n_heads + c.n_kv_heads) * hd
+        w = Weights(lc, self.embed, self.lm_head[rank * lc.vocab:(rank + 1) * lc.vocab].contiguous(),
+                    self.final_norm, cos_sin=self.cos_sin)
+        for l in range(c.n_layers):
+            qkv = self.w_qkv[l]
+            w.w_qkv.append(torch.cat([qkv[qo + rank * hq * hd: qo + (rank + 1) * hq * hd],
+                                      qkv[ko + rank * hkv * hd: ko + (rank + 1) * hkv * hd],
+                                      qkv[vo + rank * hkv * hd: vo + (rank + 1) * hkv * hd]]).contiguous())
+            w.w_o.append(self.w_o[l][:, rank * hq * hd:(rank + 1) * hq * hd].contiguous())
+            w.w_gate_up.append(self.w_gate_up[l][2 * rank * f: 2 * (rank + 1) * f].contiguous())
+            w.w_down.append(self.w_down[l][:, rank * f:(rank + 1) * f].contiguous())
+        w.ln1, w.ln2, w.q_norm, w.k_norm = self.ln1, self.ln2, self.q_norm, self.k_norm
+        return w
+
+    @staticmethod
+    def random_init_sharded(cfg: ModelConfig, device, seed: int, rank: int, size: int) -> "Weights":
+        """random_init(...).shard(rank, size) without ever holding more than one full matrix:
+        every rank draws the same full tensors in the same order and keeps its slice."""
+        if size == 1:
+            return Weights.random_init(cfg, device, seed)
+        g = torch.Generator(device=device)
+        g.manual_seed(seed)
+        lc = cfg.shard(size)
+        hd = cfg.head_dim
+
+        def lin(n, k):
+            t = torch.empty(n, k, dtype=torch.bfloat16, device=device)
+            t.normal_(0.0, 0.02, generator=g)
+            return t
+
+        ones = lambda n: torch.ones(n, dtype=torch.float32, device=device)
+        embed = lin(cfg.vocab, cfg.d_model)
+        full_head = embed if cfg.tie_embeddings else lin(cfg.vocab, cfg.d_model)
+        w = Weights(lc, embed, full_head[rank * lc.vocab:(rank + 1) * lc.vocab].contiguous(), ones(cfg.d_model))
+        del full_head
+        one = Weights(ModelConfig(**{**cfg.__dict__, "n_layers": 1}), embed, embed, w.final_norm)
+        for _ in range(cfg.n_layers):
+            w.ln1.append(ones(cfg.d_model))
+            w.ln2.append(ones(cfg.d_model))
+            one.w_qkv, one.w_o = [lin(cfg.qkv_dim, cfg.d_model)], [lin(cfg.d_model, cfg.n_heads * hd)]
+            one.w_gate_up, one.w_down = [lin(2 * cfg.d_ff, cfg.d_model)], [lin(cfg.d_model, cfg.d_ff)]
+            sh = one.shard(rank, size)
+            w.w_qkv += sh.w_qkv
+            w.w_o += sh.w_o
+            w.w_gate_up += sh.w_gate_up
+            w.w_down += sh.w_down
+            if cfg.qk_norm:
+                w.q_norm.append(ones(hd))
+                w.k_norm.append(ones(hd))
+        w.cos_sin = rope_table(cfg, device)
+        return w
+
     @staticmethod
     def random_init(cfg: ModelConfig, device, seed: int = 0) -> "Weights":
         """transformers-default init generated on the device (bench: 14B would need 59 GB of
@@ -188,7 +261,7 @@ def _ptr_array(tensors):
 class ModelHandle:
     """Host-side bcg_model struct (include/bcg_b200.h) pointing at `Weights` + per-layer KV."""
 
-    def __init__(self, w: Weights, kv_cache_layers: list, page_size: int = 16):
+    def __init__(self, w: Weights, kv_cache_layers: list, page_size: int = 16, tp_size: int = 1):
         cfg = w.cfg
         self.w = w
         self.kv = kv_cache_layers
@@ -211,4 +284,5 @@ class ModelHandle:
         self._keep.append(arr)
         m.kv_cache = C.cast(arr, C.POINTER(C.c_void_p))
         m.cos_sin = w.cos_sin.data_ptr()
+        m.tp_size = tp_size
         self.struct = m

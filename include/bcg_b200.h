@@ -134,7 +134,7 @@ int bcg_prefill_attn_paged(const void* q, const void* kv_cache, const int* block
  * accept_token/stop bookkeeping (vllm v1/sample/sampler.py:91,223-297,
  * v1/sample/ops/topk_topp_sampler.py:395-416, v1/structured_output/backend_xgrammar.py:148-192). */
 typedef struct bcg_sampler_args {
-  const float* logits;     /* [B, ld_logits] */
+  const float* logits;     /* [B, ld_logits]; or vocab-sharded, see shard_v */
   long long ld_logits;
   int B;
   int V;                   /* multiple of 4 */
@@ -166,15 +166,31 @@ typedef struct bcg_sampler_args {
   int* slot_map;             /* [B] */
   const int* block_table;    /* [B, max_blocks_per_seq] */
   int* n_active;             /* [1] number of unfinished rows after this call, or NULL */
+  /* vocab-parallel logits as NCCL all-gather leaves them: shard_v > 0 means token i of row b is at
+   * logits[(i / shard_v) * shard_stride + b * shard_v + i % shard_v]; 0 = plain [B, ld_logits] */
+  int shard_v;
+  long long shard_stride;
 } bcg_sampler_args;
 
 /* Launches the sampler described above on `stream` (stands in for xgrammar's mask apply + vLLM's
  * Sampler + accept_token bookkeeping).  `args` is a HOST struct of device pointers. */
 int bcg_mask_sample(const bcg_sampler_args* args, void* stream);
 
+/* Tensor parallelism (Qwen3-32B TP=8, Mistral-22B TP=2 in the reference's presets): one process per
+ * GPU, one NCCL communicator per process.  Rank 0 obtains an id with bcg_tp_unique_id, ships the
+ * 128 bytes to the other ranks by any means, everyone calls bcg_tp_init (collective).  The model
+ * steps then all-reduce the outputs of the row-parallel o / down projections (2 per layer) and
+ * all-gather the vocab-parallel logits, standing in for vLLM's TP collectives
+ * (vllm_agent.py:131,141-142).  libnccl.so.2 is resolved at run time. */
+int bcg_tp_unique_id(void* out_128_bytes /* host */);
+int bcg_tp_init(const void* id_128_bytes /* host */, int rank, int size);
+int bcg_tp_shutdown(void);
+
 /* Whole-model steps: the layer stack launched from C++ on one stream so a decode step is one
  * host call (captured into a CUDA graph by the engine).  See DESIGN.md §4. */
 typedef struct bcg_model {
+  /* With tensor parallelism n_heads, n_kv_heads, d_ff and vocab are THIS RANK's shard sizes
+   * (column-parallel qkv / gate_up, row-parallel o / down, vocab-parallel lm_head). */
   int n_layers, d_model, n_heads, n_kv_heads, head_dim, d_ff, vocab;
   float rms_eps;
   int page_size;
@@ -191,6 +207,7 @@ typedef struct bcg_model {
   const float* const* k_norm;
   void* const* kv_cache;         /* per-layer cache base */
   const float* cos_sin;          /* [max_pos][128] */
+  int tp_size;                   /* 1, or the size given to bcg_tp_init */
 } bcg_model;
 
 typedef struct bcg_workspace {
@@ -207,7 +224,8 @@ typedef struct bcg_workspace {
   float* attn_scratch_ml;
   int* attn_counters;  /* int32 [B_max * n_kv_heads], zero-initialised once */
   int max_splits;
-  float* logits;      /* fp32 [B_max, vocab] */
+  float* logits;      /* fp32 [B_max, vocab]; with TP: [tp][B][vocab/tp] as all-gathered */
+  float* logits_local; /* fp32 [B_max, vocab/tp], only with TP */
   void* xn_last;      /* bf16 [B_max, d_model] */
   int T_max, B_max;
 } bcg_workspace;
