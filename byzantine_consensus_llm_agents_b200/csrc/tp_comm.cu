@@ -44,7 +44,9 @@ static int load_nccl() {
   }
   g_tp.get_unique_id = reinterpret_cast<GetUniqueIdFn>(dlsym(h, "ncclGetUniqueId"));
   g_tp.comm_init_rank = reinterpret_cast<CommInitRankFn>(dlsym(h, "ncclCommInitRank"));
-  g_tp.comm_destroy = reinterpret_cast<CommDestroyFn>(dlsym(h, "ncclCommDestroy"));
+  // Teardown uses ncclCommAbort: ncclCommDestroy blocks while CUDA graphs that contain NCCL
+  // kernels are still alive (the engine's captured decode steps), abort never does.
+  g_tp.comm_destroy = reinterpret_cast<CommDestroyFn>(dlsym(h, "ncclCommAbort"));
   g_tp.all_reduce = reinterpret_cast<AllReduceFn>(dlsym(h, "ncclAllReduce"));
   g_tp.all_gather = reinterpret_cast<AllGatherFn>(dlsym(h, "ncclAllGather"));
   g_tp.error_string = reinterpret_cast<GetErrorStringFn>(dlsym(h, "ncclGetErrorString"));

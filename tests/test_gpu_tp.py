@@ -22,6 +22,8 @@ def _free_port():
 
 
 def _worker(rank, size, port, family, ret):
+    import faulthandler
+    faulthandler.dump_traceback_later(50, exit=True)     # a hung collective must not eat the GPU budget
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=size)
     try:
@@ -63,14 +65,16 @@ def _worker(rank, size, port, family, ret):
                 ref = full_logits(hf, p + f[:-1])[len(p) - 1:]
                 worst = max(worst, (got[:, b] - ref).abs().max().item())
             out["worst"] = worst
-            # the same requests on a single-GPU engine
-            tp.shutdown_comm()
+            # the same requests on a single-GPU engine (tp_size = 1: no collectives are issued)
             solo = Engine(cfg, full, tk, max_model_len=1024, max_rows=8, prefill_tokens=2048, kv_pages=400,
                           device="cuda:0")
             out["solo"] = [r.token_ids for r in solo.generate([Request("", schema, 0.0, 24, prompt_ids=p)
                                                                for p in prompts])]
         ret[rank] = out
+        eng.close()
+        torch.cuda.synchronize()
         dist.barrier()
+        tp.shutdown_comm()
     finally:
         dist.destroy_process_group()
 
