@@ -264,6 +264,9 @@ def main():
     ap.add_argument("--honest", type=int, default=8)
     ap.add_argument("--byzantine", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--tp", type=int, default=1,
+                    help="tensor_parallel_size of each replica (ranks beyond the first are spawned by "
+                         "the adapter, like vLLM's mp executor); use with --gpus == --tp")
     ap.add_argument("--pdl", type=int, default=int(os.environ.get("BCG_B200_PDL", "1")),
                     help="programmatic dependent launch for the decode step (1 = on)")
     a = ap.parse_args()
@@ -278,7 +281,8 @@ def main():
                           "one game round per step (decide T=0.5/300 tok + vote T=0.3/200 tok, reference "
                           "retry schedule), recorded steady-state reference prompts",
               "agents": n_agents, "rounds_recorded": len(rounds), "pdl": bool(a.pdl),
-              "parallelism": f"dp{world} (one independent game per GPU)" if world > 1 else "single GPU",
+              "parallelism": (f"tp{a.tp} (one replica, NCCL all-reduce)" if a.tp > 1 else
+                              f"dp{world} (one independent game per GPU)" if world > 1 else "single GPU"),
               "l2": "per-step inputs (27.98 GB of weights per decode step) exceed the 126 MB L2"}
 
     if a.impl == "reference":
@@ -314,6 +318,8 @@ def main():
     model_config = {"max_model_len": 8192, "gpu_memory_utilization": 0.9, "tensor_parallel_size": 1,
                     "max_num_seqs": 4, "disable_qwen3_thinking": True, "device": f"cuda:{local_rank}",
                     "seed": 1000 + rank, "engine_max_rows": max(16, n_agents), "pdl": bool(a.pdl)}
+    if a.tp > 1:
+        model_config["tensor_parallel_size"] = a.tp
     t_load = time.perf_counter()
     agent = VA.VLLMAgent("agent_0", model_name, model_config)
     engine = agent.llm.engine
@@ -353,13 +359,14 @@ def main():
         # whole-step decode roofline: W + sum_rows S*KVB per step
         avg_rows = d["generated_tokens"] / max(1, d["decode_steps"])
         avg_ctx = (d["prompt_tokens"] / max(1, d["prompts"])) + 0.5 * (gen / max(1, d["prompts"]))
-        bytes_per_step = cfg.decode_weight_bytes() + avg_rows * avg_ctx * cfg.kv_bytes_per_token
+        # per GPU: under TP every rank streams 1/tp of the weights and of the KV heads
+        bytes_per_step = (cfg.decode_weight_bytes() + avg_rows * avg_ctx * cfg.kv_bytes_per_token) / a.tp
         step_s = d["decode_s"] / max(1, steps)
         dec_ach = bytes_per_step / step_s / 1e9 if steps else 0.0
         pf_flops = d["prefill_tokens"] * cfg.prefill_gemm_flops_per_token()
         line = {
             "metric": "agent_steps_per_sec", "value": round(total_agent_steps / dev_max, 4),
-            "unit": "agent-steps/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "unit": "agent-steps/s", "n_gpus": world * a.tp, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": round(1e3 * wall_max / a.steps, 2), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": config,
@@ -383,8 +390,9 @@ def main():
                          "host_ms": round(1e3 * (wall - dev_s) / a.steps, 1)},
             "model_load_s": round(t_load, 1), "clocks": clk,
         }
-        line["roofline"] = kernel_roofline(engine, n_agents, hbm_peak, peak_kind)
-        if world == 1 and not a.no_cpu_baseline:
+        if a.tp == 1:
+            line["roofline"] = kernel_roofline(engine, n_agents, hbm_peak, peak_kind)
+        if world == 1 and a.tp == 1 and not a.no_cpu_baseline:
             VA.VLLMAgent.shutdown()
             try:
                 line["cpu_baseline"] = cpu_baseline(a.model, rounds, n_agents)
@@ -392,6 +400,8 @@ def main():
                 line["cpu_baseline"] = {"value": None, "unit": "agent-steps/s", "cores": os.cpu_count(),
                                         "kind": "port", "sample": f"failed: {e}"}
         print(json.dumps(line), flush=True)
+    if a.tp > 1:
+        VA.VLLMAgent.shutdown()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

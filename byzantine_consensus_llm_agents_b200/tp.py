@@ -50,3 +50,104 @@ def worker_loop(engine, group=None, src: int = 0) -> None:
         if isinstance(reqs, str) and reqs == STOP:
             return
         engine.generate(reqs)
+
+
+# ---------------------------------------------------------------------------------------------
+# Single-process front end: spawn the other ranks, as vLLM's `mp` executor does for the reference
+# ---------------------------------------------------------------------------------------------
+def _build_engine(model_name: str, model_config: dict, rank: int, size: int):
+    """Engine holding rank's shard of the model on cuda:<first_device + rank>."""
+    import os
+
+    from . import model as M
+    from . import vllm_agent as VA
+    from .engine import Engine
+    from .tokenizer import get_tokenizer
+    key = model_name.lower()
+    dev_index = int(str(model_config.get("device", "cuda:0")).split(":")[-1]) + rank
+    device = torch.device(f"cuda:{dev_index}")
+    torch.cuda.set_device(device)
+    if key in VA._REGISTRY:
+        cfg, factory = VA._REGISTRY[key]
+        weights = factory(cfg, device).shard(rank, size)
+    else:
+        cfg = M.config_for(model_name)
+        seed = int(model_config.get("weight_seed", os.environ.get("BCG_B200_WEIGHT_SEED", 0)))
+        weights = M.Weights.random_init_sharded(cfg, device, seed, rank, size)
+    tok = get_tokenizer(cfg.family, cfg.vocab)
+    eng = Engine(cfg, weights, tok,
+                 max_model_len=int(model_config.get("max_model_len", 8192)),
+                 gpu_memory_utilization=float(model_config.get("gpu_memory_utilization", 0.85)),
+                 max_rows=int(model_config.get("engine_max_rows", 64)),
+                 kv_pages=model_config.get("kv_pages"),
+                 base_seed=int(model_config.get("seed", os.environ.get("BCG_B200_SEED", 0))),
+                 device=str(device), use_cuda_graph=bool(model_config.get("use_cuda_graph", True)),
+                 pdl=bool(model_config.get("pdl", False)), tp_rank=rank, tp_size=size)
+    return cfg, tok, eng
+
+
+def _spawned_worker(rank: int, size: int, port: int, model_name: str, model_config: dict, registry: dict):
+    import os
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    from . import vllm_agent as VA
+    VA._REGISTRY.update(registry)
+    dist.init_process_group("gloo", rank=rank, world_size=size)
+    try:
+        init_comm(rank, size)
+        _, _, eng = _build_engine(model_name, model_config, rank, size)
+        worker_loop(eng)
+        eng.close()
+        torch.cuda.synchronize()
+        shutdown_comm()
+    finally:
+        dist.destroy_process_group()
+
+
+class SpawnedTP:
+    """Rank 0 of a tensor-parallel replica living in the caller's process; ranks 1.. are spawned
+    (one per additional GPU) and driven over a private gloo group."""
+
+    def __init__(self, model_name: str, model_config: dict, size: int):
+        import os
+        import socket
+
+        import torch.multiprocessing as mp
+
+        from . import vllm_agent as VA
+        if dist.is_available() and dist.is_initialized():
+            raise L.BcgError("tensor_parallel_size > 1 from a process that already runs torch.distributed: "
+                             "launch one TP replica per process group instead (see bench.py --tp)")
+        if torch.cuda.device_count() < size:
+            raise L.BcgError(f"tensor_parallel_size={size} needs {size} GPUs, {torch.cuda.device_count()} visible")
+        with socket.socket() as s:
+            s.bind(("127.0.0.1", 0))
+            port = s.getsockname()[1]
+        ctx = mp.get_context("spawn")
+        self.procs = [ctx.Process(target=_spawned_worker,
+                                  args=(r, size, port, model_name, dict(model_config), dict(VA._REGISTRY)),
+                                  daemon=True) for r in range(1, size)]
+        for p in self.procs:
+            p.start()
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+        dist.init_process_group("gloo", rank=0, world_size=size)
+        init_comm(0, size)
+        self.cfg, self.tokenizer, self.engine = _build_engine(model_name, model_config, 0, size)
+        self.size = size
+
+    def generate(self, reqs):
+        broadcast_requests(reqs)
+        return self.engine.generate(reqs)
+
+    def close(self):
+        try:
+            broadcast_requests(STOP)
+            self.engine.close()
+            torch.cuda.synchronize()
+            shutdown_comm()
+        finally:
+            if dist.is_initialized():
+                dist.destroy_process_group()
+            for p in self.procs:
+                p.join(timeout=30)
+                if p.is_alive():
+                    p.terminate()

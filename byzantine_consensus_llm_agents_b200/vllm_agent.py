@@ -77,8 +77,16 @@ class B200LLM:
         from .engine import Engine
         from .tokenizer import get_tokenizer
 
-        if int(model_config.get("tensor_parallel_size", 1)) != 1:
-            raise NotImplementedError("tensor_parallel_size > 1 is not built yet (DESIGN.md §7)")
+        self.data_parallel = bool(model_config.get("data_parallel", False))
+        self.tp = None
+        tp_size = int(model_config.get("tensor_parallel_size", 1))
+        if tp_size > 1:
+            # the reference has vLLM spawn `mp` workers here (vllm_agent.py:141-142); same shape:
+            # this process is rank 0, ranks 1..tp-1 are spawned, one per additional GPU
+            from .tp import SpawnedTP
+            self.tp = SpawnedTP(model_name, model_config, tp_size)
+            self.cfg, self.tokenizer, self.engine = self.tp.cfg, self.tp.tokenizer, self.tp.engine
+            return
         key = model_name.lower()
         if key in _REGISTRY:
             cfg, factory = _REGISTRY[key]
@@ -87,7 +95,6 @@ class B200LLM:
             seed = int(model_config.get("weight_seed", os.environ.get("BCG_B200_WEIGHT_SEED", 0)))
             factory = lambda c, dev: M.Weights.random_init(c, dev, seed=seed)
         device = model_config.get("device", "cuda:0")
-        self.data_parallel = bool(model_config.get("data_parallel", False))
         self.cfg = cfg
         self.tokenizer = get_tokenizer(cfg.family, cfg.vocab)
         weights = factory(cfg, torch.device(device))
@@ -107,6 +114,9 @@ class B200LLM:
         from . import dp
         from .engine import Request, row_seed
         call = self.engine.calls
+        if self.tp is not None:
+            reqs = [Request(p, s, float(temperature), int(max_tokens)) for p, s in zip(prompts, schemas)]
+            return [r.text for r in self.tp.generate(reqs)]
         if not self.data_parallel or dp.dist_info()[1] == 1:
             reqs = [Request(p, s, float(temperature), int(max_tokens)) for p, s in zip(prompts, schemas)]
             return [r.text for r in self.engine.generate(reqs)]
@@ -122,7 +132,10 @@ class B200LLM:
         return texts
 
     def close(self) -> None:
-        self.engine.close()
+        if self.tp is not None:
+            self.tp.close()
+        else:
+            self.engine.close()
 
 
 def _brace_match(text: str) -> Optional[Dict[str, Any]]:

@@ -49,6 +49,7 @@ def _make_agent(data_parallel):
     llm = VA.B200LLM.__new__(VA.B200LLM)
     llm.engine = _FakeEngine()
     llm.data_parallel = data_parallel
+    llm.tp = None
     cfg = {"max_model_len": 64}
     VA.VLLMAgent._shared_llm, VA.VLLMAgent._shared_model_name, VA.VLLMAgent._shared_model_config = llm, "Qwen/Qwen3-8B", cfg
     return VA.VLLMAgent("a", "Qwen/Qwen3-8B", cfg), llm
