@@ -283,7 +283,7 @@ def main():
               "agents": n_agents, "rounds_recorded": len(rounds), "pdl": bool(a.pdl),
               "parallelism": (f"tp{a.tp} (one replica, NCCL all-reduce)" if a.tp > 1 else
                               f"dp{world} (one independent game per GPU)" if world > 1 else "single GPU"),
-              "l2": "per-step inputs (27.98 GB of weights per decode step) exceed the 126 MB L2"}
+              "l2": "per-step inputs (all layer weights, tens of GB per decode step) exceed the 126 MB L2"}
 
     if a.impl == "reference":
         if rank != 0:
@@ -363,7 +363,7 @@ def main():
         bytes_per_step = (cfg.decode_weight_bytes() + avg_rows * avg_ctx * cfg.kv_bytes_per_token) / a.tp
         step_s = d["decode_s"] / max(1, steps)
         dec_ach = bytes_per_step / step_s / 1e9 if steps else 0.0
-        pf_flops = d["prefill_tokens"] * cfg.prefill_gemm_flops_per_token()
+        pf_flops = d["prefill_tokens"] * cfg.prefill_gemm_flops_per_token() / a.tp   # per GPU
         line = {
             "metric": "agent_steps_per_sec", "value": round(total_agent_steps / dev_max, 4),
             "unit": "agent-steps/s", "n_gpus": world * a.tp, "steps": a.steps, "warmup": a.warmup,

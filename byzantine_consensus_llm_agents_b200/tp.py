@@ -55,6 +55,10 @@ def worker_loop(engine, group=None, src: int = 0) -> None:
 # ---------------------------------------------------------------------------------------------
 # Single-process front end: spawn the other ranks, as vLLM's `mp` executor does for the reference
 # ---------------------------------------------------------------------------------------------
+def _device_for(model_config: dict, rank: int) -> torch.device:
+    return torch.device(f"cuda:{int(str(model_config.get('device', 'cuda:0')).split(':')[-1]) + rank}")
+
+
 def _build_engine(model_name: str, model_config: dict, rank: int, size: int):
     """Engine holding rank's shard of the model on cuda:<first_device + rank>."""
     import os
@@ -93,6 +97,7 @@ def _spawned_worker(rank: int, size: int, port: int, model_name: str, model_conf
     VA._REGISTRY.update(registry)
     dist.init_process_group("gloo", rank=rank, world_size=size)
     try:
+        torch.cuda.set_device(_device_for(model_config, rank))   # NCCL binds to the current device
         init_comm(rank, size)
         _, _, eng = _build_engine(model_name, model_config, rank, size)
         worker_loop(eng)
@@ -130,6 +135,7 @@ class SpawnedTP:
             p.start()
         os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
         dist.init_process_group("gloo", rank=0, world_size=size)
+        torch.cuda.set_device(_device_for(model_config, 0))
         init_comm(0, size)
         self.cfg, self.tokenizer, self.engine = _build_engine(model_name, model_config, 0, size)
         self.size = size
