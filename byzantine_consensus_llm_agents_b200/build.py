@@ -28,6 +28,7 @@ SOURCES = [
     "sampler.cu",
     "model_step.cu",
     "tp_comm.cu",
+    "tp_reduce_norm.cu",
 ]
 
 NVCC_FLAGS = [

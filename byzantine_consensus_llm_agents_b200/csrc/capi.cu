@@ -104,6 +104,11 @@ int bcg_mask_sample(const bcg_sampler_args* args, void* stream) {
 int bcg_tp_unique_id(void* out_128_bytes) { return tp_unique_id(out_128_bytes); }
 int bcg_tp_init(const void* id_128_bytes, int rank, int size) { return tp_init(id_128_bytes, rank, size); }
 int bcg_tp_shutdown(void) { return tp_shutdown(); }
+int bcg_tp_symm_create(long long bytes, void* handle_out_64_bytes) {
+  void* local = nullptr;
+  return tp_symm_create(bytes, handle_out_64_bytes, &local);
+}
+int bcg_tp_symm_open(const void* handles, int rank, int size) { return tp_symm_open(handles, rank, size); }
 
 int bcg_model_prefill(const bcg_model* m, const bcg_workspace* ws, const int* ids,
                       const int* positions, const int* slot_map, const int* block_table,

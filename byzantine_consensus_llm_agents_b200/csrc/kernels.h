@@ -54,5 +54,15 @@ int tp_size();
 int tp_rank();
 int tp_all_reduce_f32(float* buf, long long count, cudaStream_t stream);
 int tp_all_gather_f32(const float* send, float* recv, long long count, cudaStream_t stream);
+int tp_symm_create(long long bytes, void* handle_out64, void** local_ptr);
+int tp_symm_open(const void* handles, int rank, int size);
+void* tp_symm_local();
+void* const* tp_symm_peers_device();
+long long tp_symm_bytes();
+// fused cross-GPU reduction + residual add + RMSNorm over peer memory (tp_reduce_norm.cu)
+int tp_signal(int slot, cudaStream_t stream);
+int tp_add_rmsnorm(float* residual, long long region_offset_floats, int n_partials, long long partial_stride,
+                   const float* w, void* xn, int slot, int T, int d, float eps, cudaStream_t stream);
+long long tp_symm_flag_floats();
 
 }  // namespace bcg

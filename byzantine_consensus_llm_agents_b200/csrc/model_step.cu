@@ -113,6 +113,18 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
     set_last_error("bcg_model_decode", "tp_size does not match bcg_tp_init, or logits_local missing");
     return BCG_ERR_ARG;
   }
+  // fused peer-memory all-reduce (tp_reduce_norm.cu) when the symmetric buffer is set up
+  const bool fused = tp > 1 && ws->tp_region_floats > 0 && tp_symm_local() != nullptr;
+  float* sym = static_cast<float*>(tp_symm_local());
+  const long long off_o = tp_symm_flag_floats(), off_dn = tp_symm_flag_floats() + ws->tp_region_floats;
+  if (fused) {
+    const long long need_sym = static_cast<long long>(s_o > s_dn ? s_o : s_dn) * B * d;
+    if (need_sym > ws->tp_region_floats ||
+        (tp_symm_flag_floats() + 2 * ws->tp_region_floats) * 4 > tp_symm_bytes()) {
+      set_last_error("bcg_model_decode", "symmetric TP buffer too small");
+      return BCG_ERR_TOO_LARGE;
+    }
+  }
   const int gf = flags & BCG_GEMM_PDL;
   // profiling aids (tools/step_ablation.py): leave one kernel family out of the step to read its
   // in-pipeline cost off the step time.  Results are garbage with any of these set.
@@ -128,6 +140,9 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
   for (int l = 0; l < m->n_layers; ++l) {
     if (l == 0) {
       BCG_TRY(embed_rmsnorm(ids, m->embed, m->ln1[0], ws->residual, ws->xn, B, d, m->rms_eps, st));
+    } else if (fused) {
+      BCG_TRY(tp_add_rmsnorm(ws->residual, off_dn, s_dn, static_cast<long long>(B) * d, m->ln1[l], ws->xn, 1,
+                             B, d, m->rms_eps, st));
     } else if (!skip_norm) {
       BCG_TRY(add_rmsnorm(ws->residual, P, 1, s_dn, static_cast<long long>(B) * d, m->ln1[l], ws->xn,
                           nullptr, B, d, m->rms_eps, st));
@@ -144,6 +159,15 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
     BCG_TRY(decode_attn_paged(ws->q, m->kv_cache[l], block_table, max_blocks, seq_lens, ws->attn,
                               ws->attn_scratch_o, ws->attn_scratch_ml, ws->attn_counters, B, hq, hkv,
                               m->page_size, ws->max_splits, scale, st));
+    if (fused) {
+      // row-parallel projection straight into the symmetric buffer; the norm kernel sums every
+      // rank's slabs from peer memory
+      BCG_TRY(gemm_bf16_tn(ws->attn, m->w_o[l], sym + off_o, B, d, hq * 128, hq * 128, hq * 128, d,
+                           BCG_EPI_F32, s_o, gf, st));
+      BCG_TRY(tp_signal(0, st));
+      BCG_TRY(tp_add_rmsnorm(ws->residual, off_o, s_o, static_cast<long long>(B) * d, m->ln2[l], ws->xn, 0, B,
+                             d, m->rms_eps, st));
+    } else {
     if (!skip_o)
     BCG_TRY(gemm_bf16_tn(ws->attn, m->w_o[l], P, B, d, hq * 128, hq * 128, hq * 128, d, BCG_EPI_F32,
                          s_o, gf, st));
@@ -153,6 +177,7 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
     if (!skip_norm)
     BCG_TRY(add_rmsnorm(ws->residual, P, 1, s_o, static_cast<long long>(B) * d, m->ln2[l], ws->xn,
                         nullptr, B, d, m->rms_eps, st));
+    }
     if (skip_gu) {
     } else if (s_gu == 1) {
       BCG_TRY(gemm_bf16_tn(ws->xn, m->w_gate_up[l], ws->act, B, 2 * ff, d, d, d, ff, BCG_EPI_SWIGLU, 1,
@@ -162,12 +187,22 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
                            gf, st));
       BCG_TRY(swiglu_reduce(P, s_gu, static_cast<long long>(B) * 2 * ff, ws->act, B, 2 * ff, st));
     }
-    if (!skip_dn)
-    BCG_TRY(gemm_bf16_tn(ws->act, m->w_down[l], P, B, d, ff, ff, ff, d, BCG_EPI_F32, s_dn, gf, st));
-    if (tp > 1) BCG_TRY(tp_all_reduce_f32(P, static_cast<long long>(s_dn) * B * d, st));
+    if (fused) {
+      BCG_TRY(gemm_bf16_tn(ws->act, m->w_down[l], sym + off_dn, B, d, ff, ff, ff, d, BCG_EPI_F32, s_dn, gf, st));
+      BCG_TRY(tp_signal(1, st));
+    } else {
+      if (!skip_dn)
+      BCG_TRY(gemm_bf16_tn(ws->act, m->w_down[l], P, B, d, ff, ff, ff, d, BCG_EPI_F32, s_dn, gf, st));
+      if (tp > 1) BCG_TRY(tp_all_reduce_f32(P, static_cast<long long>(s_dn) * B * d, st));
+    }
   }
-  BCG_TRY(add_rmsnorm(ws->residual, P, 1, s_dn, static_cast<long long>(B) * d, m->final_norm,
-                      ws->xn_last, nullptr, B, d, m->rms_eps, st));
+  if (fused) {
+    BCG_TRY(tp_add_rmsnorm(ws->residual, off_dn, s_dn, static_cast<long long>(B) * d, m->final_norm,
+                           ws->xn_last, 1, B, d, m->rms_eps, st));
+  } else {
+    BCG_TRY(add_rmsnorm(ws->residual, P, 1, s_dn, static_cast<long long>(B) * d, m->final_norm,
+                        ws->xn_last, nullptr, B, d, m->rms_eps, st));
+  }
   if (tp > 1) {
     BCG_TRY(gemm_bf16_tn(ws->xn_last, m->lm_head, ws->logits_local, B, m->vocab, d, d, d, m->vocab,
                          BCG_EPI_F32, 1, gf, st));

@@ -5,6 +5,7 @@
 // libnccl is the one PyTorch already loaded; it is resolved with dlopen so the library has no
 // link-time dependency on it and single-GPU users never touch it.
 #include <dlfcn.h>
+#include <string.h>
 
 #include "common.cuh"
 #include "kernels.h"
@@ -32,7 +33,17 @@ static struct {
   int rank = 0, size = 1;
 } g_tp;
 
+constexpr int kMaxTp = 8;
 constexpr int kNcclFloat32 = 7;
+
+// symmetric peer memory for the fused decode all-reduce (tp_reduce_norm.cu)
+static struct {
+  void* local = nullptr;
+  void* peers[kMaxTp] = {};
+  long long bytes = 0;
+  void** d_peers = nullptr;   // device copy of peers[]
+} g_sym;
+
 constexpr int kNcclSum = 0;
 
 static int load_nccl() {
@@ -97,6 +108,15 @@ int tp_init(const void* id128, int rank, int size) {
 }
 
 int tp_shutdown() {
+  for (int r = 0; r < kMaxTp; ++r) {
+    if (g_sym.peers[r] && g_sym.peers[r] != g_sym.local) cudaIpcCloseMemHandle(g_sym.peers[r]);
+    g_sym.peers[r] = nullptr;
+  }
+  if (g_sym.d_peers) cudaFree(g_sym.d_peers);
+  if (g_sym.local) cudaFree(g_sym.local);
+  g_sym.d_peers = nullptr;
+  g_sym.local = nullptr;
+  g_sym.bytes = 0;
   if (g_tp.comm) {
     g_tp.comm_destroy(g_tp.comm);
     g_tp.comm = nullptr;
@@ -105,6 +125,50 @@ int tp_shutdown() {
   g_tp.size = 1;
   return BCG_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Symmetric peer memory for the fused decode all-reduce (tp_reduce_norm.cu)
+// ---------------------------------------------------------------------------------------------
+int tp_symm_create(long long bytes, void* handle_out64, void** local_ptr) {
+  if (bytes <= 0 || !handle_out64 || !local_ptr) return BCG_ERR_ARG;
+  if (g_sym.local) {
+    set_last_error("bcg_tp_symm_create", "already created");
+    return BCG_ERR_ARG;
+  }
+  BCG_CUDA_CHECK(cudaMalloc(&g_sym.local, static_cast<size_t>(bytes)));
+  BCG_CUDA_CHECK(cudaMemset(g_sym.local, 0, static_cast<size_t>(bytes)));
+  cudaIpcMemHandle_t h;
+  BCG_CUDA_CHECK(cudaIpcGetMemHandle(&h, g_sym.local));
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  memcpy(handle_out64, &h, 64);
+  g_sym.bytes = bytes;
+  *local_ptr = g_sym.local;
+  return BCG_OK;
+}
+
+// handles: [size][64] bytes in rank order (this rank's own entry is ignored)
+int tp_symm_open(const void* handles, int rank, int size) {
+  if (!handles || !g_sym.local || size < 1 || size > kMaxTp || rank < 0 || rank >= size) {
+    set_last_error("bcg_tp_symm_open", "bad arguments (tp size <= 8) or bcg_tp_symm_create not called");
+    return BCG_ERR_ARG;
+  }
+  for (int r = 0; r < size; ++r) {
+    if (r == rank) {
+      g_sym.peers[r] = g_sym.local;
+      continue;
+    }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, static_cast<const char*>(handles) + 64 * r, 64);
+    BCG_CUDA_CHECK(cudaIpcOpenMemHandle(&g_sym.peers[r], h, cudaIpcMemLazyEnablePeerAccess));
+  }
+  BCG_CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&g_sym.d_peers), sizeof(void*) * kMaxTp));
+  BCG_CUDA_CHECK(cudaMemcpy(g_sym.d_peers, g_sym.peers, sizeof(void*) * kMaxTp, cudaMemcpyHostToDevice));
+  return BCG_OK;
+}
+
+void* tp_symm_local() { return g_sym.local; }
+void* const* tp_symm_peers_device() { return g_sym.d_peers; }
+long long tp_symm_bytes() { return g_sym.bytes; }
 
 int tp_size() { return g_tp.comm ? g_tp.size : 1; }
 int tp_rank() { return g_tp.comm ? g_tp.rank : 0; }

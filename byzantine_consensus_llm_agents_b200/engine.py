@@ -146,7 +146,7 @@ class Engine:
                  max_rows: int = 64, prefill_tokens: int = 16384, kv_pages: Optional[int] = None,
                  gpu_memory_utilization: float = 0.9, base_seed: int = 0, device: str = "cuda:0",
                  enable_prefix_cache: bool = True, use_cuda_graph: bool = True, pdl: bool = False,
-                 tp_rank: int = 0, tp_size: int = 1):
+                 tp_rank: int = 0, tp_size: int = 1, tp_fused_allreduce: bool = True, tp_group=None):
         """`cfg` is the FULL architecture; with tp_size > 1 `weights` must be this rank's shard
         (Weights.shard / random_init_sharded) and bcg_tp_init must have been called (collective)."""
         if not torch.cuda.is_available():
@@ -202,6 +202,13 @@ class Engine:
         ws.max_splits = self.max_splits_cap
         ws.logits, ws.xn_last, ws.T_max, ws.B_max = b["logits"].data_ptr(), b["xn_last"].data_ptr(), T, B
         ws.logits_local = b["logits_local"].data_ptr() if tp_size > 1 else None
+        ws.tp_region_floats = 0
+        if tp_size > 1 and tp_fused_allreduce:
+            # decode all-reduces fused into the norm kernels over NVLink peer memory
+            from . import tp as _tp
+            region = max(splits[1], splits[3]) * B * d
+            _tp.setup_symmetric(4 * (256 + 2 * region), tp_rank, tp_size, tp_group)
+            ws.tp_region_floats = region
         self.ws = ws
         # ---- KV pages
         page_bytes = 2 * lc.n_kv_heads * PAGE * 128 * 2 * cfg.n_layers

@@ -60,7 +60,8 @@ class Workspace(C.Structure):
         ("delta", vp), ("partials", vp), ("partials_floats", C.c_longlong),
         ("attn_scratch_o", vp), ("attn_scratch_ml", vp), ("attn_counters", vp),
         ("max_splits", C.c_int),
-        ("logits", vp), ("logits_local", vp), ("xn_last", vp), ("T_max", C.c_int), ("B_max", C.c_int),
+        ("logits", vp), ("logits_local", vp), ("tp_region_floats", C.c_longlong), ("xn_last", vp),
+        ("T_max", C.c_int), ("B_max", C.c_int),
     ]
 
 
@@ -87,6 +88,8 @@ _SIGS = {
     "bcg_tp_unique_id": (C.c_int, [vp]),
     "bcg_tp_init": (C.c_int, [vp, C.c_int, C.c_int]),
     "bcg_tp_shutdown": (C.c_int, []),
+    "bcg_tp_symm_create": (C.c_int, [C.c_longlong, vp]),
+    "bcg_tp_symm_open": (C.c_int, [vp, C.c_int, C.c_int]),
     "bcg_model_prefill": (C.c_int, [C.POINTER(Model), C.POINTER(Workspace), vp, vp, vp, vp, C.c_int,
                                     vp, C.c_int, vp, C.c_int, C.c_int, vp]),
     "bcg_model_decode": (C.c_int, [C.POINTER(Model), C.POINTER(Workspace), vp, vp, vp, vp, vp,

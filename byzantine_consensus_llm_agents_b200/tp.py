@@ -32,6 +32,18 @@ def init_comm(rank: int, size: int, group=None, src: int = 0) -> None:
     L.check(lib.bcg_tp_init(ident, rank, size), "bcg_tp_init")
 
 
+def setup_symmetric(nbytes: int, rank: int, size: int, group=None) -> None:
+    """Collective: every rank allocates the symmetric decode buffer and maps its peers' (cudaIpc)."""
+    lib = L.load()
+    mine = (C.c_char * 64)()
+    L.check(lib.bcg_tp_symm_create(nbytes, mine), "bcg_tp_symm_create")
+    handles = [None] * size
+    dist.all_gather_object(handles, bytes(mine), group=group)
+    blob = (C.c_char * (64 * size)).from_buffer_copy(b"".join(handles))
+    L.check(lib.bcg_tp_symm_open(blob, rank, size), "bcg_tp_symm_open")
+    dist.barrier(group=group)
+
+
 def shutdown_comm() -> None:
     L.load().bcg_tp_shutdown()
 

@@ -185,6 +185,14 @@ int bcg_mask_sample(const bcg_sampler_args* args, void* stream);
 int bcg_tp_unique_id(void* out_128_bytes /* host */);
 int bcg_tp_init(const void* id_128_bytes /* host */, int rank, int size);
 int bcg_tp_shutdown(void);
+/* Optional fast path for the DECODE step: a symmetric buffer every rank of the replica maps
+ * (cudaIpc over NVLink).  With it the two per-layer all-reduces are fused into the norm kernel
+ * that follows them (peer loads + flags, no NCCL launch); without it the decode step uses NCCL.
+ * create: cudaMalloc's `bytes` (the only allocation this library ever makes; freed by
+ * bcg_tp_shutdown) and returns the 64-byte IPC handle; open: takes all ranks' handles in rank
+ * order.  bytes = 4 * (256 + 2 * tp_region_floats) with tp_region_floats as in bcg_workspace. */
+int bcg_tp_symm_create(long long bytes, void* handle_out_64_bytes /* host */);
+int bcg_tp_symm_open(const void* handles_size_x_64_bytes /* host */, int rank, int size);
 
 /* Whole-model steps: the layer stack launched from C++ on one stream so a decode step is one
  * host call (captured into a CUDA graph by the engine).  See DESIGN.md §4. */
@@ -226,6 +234,8 @@ typedef struct bcg_workspace {
   int max_splits;
   float* logits;      /* fp32 [B_max, vocab]; with TP: [tp][B][vocab/tp] as all-gathered */
   float* logits_local; /* fp32 [B_max, vocab/tp], only with TP */
+  long long tp_region_floats; /* > 0: fused peer-memory all-reduce in decode; floats per slot of the
+                                 symmetric buffer, >= max(splits_o, splits_down) * B_max * d_model */
   void* xn_last;      /* bf16 [B_max, d_model] */
   int T_max, B_max;
 } bcg_workspace;

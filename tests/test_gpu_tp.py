@@ -21,7 +21,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, size, port, family, ret):
+def _worker(rank, size, port, family, fused, ret):
     import faulthandler
     faulthandler.dump_traceback_later(50, exit=True)     # a hung collective must not eat the GPU budget
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
@@ -44,7 +44,8 @@ def _worker(rank, size, port, family, ret):
         tk = get_tokenizer(cfg.family, cfg.vocab)
         tp.init_comm(rank, size)
         eng = Engine(cfg, full.shard(rank, size), tk, max_model_len=1024, max_rows=8, prefill_tokens=2048,
-                     kv_pages=400, device=f"cuda:{rank}", tp_rank=rank, tp_size=size)
+                     kv_pages=400, device=f"cuda:{rank}", tp_rank=rank, tp_size=size,
+                     tp_fused_allreduce=fused)
         rng = np.random.default_rng(0)
         lo, hi = tk.regular_range
         lens = [5, 70, 300]
@@ -80,11 +81,13 @@ def _worker(rank, size, port, family, ret):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("family", ["qwen3", "mistral"])
-def test_tp2_matches_oracle_and_tp1(family):
+@pytest.mark.parametrize("family,fused", [("qwen3", True), ("mistral", True), ("qwen3", False)],
+                         ids=["qwen3-fused", "mistral-fused", "qwen3-nccl"])
+def test_tp2_matches_oracle_and_tp1(family, fused):
+    """fused = decode all-reduces inside the norm kernels over peer memory; otherwise NCCL."""
     mgr = mp.Manager()
     ret = mgr.dict()
-    mp.spawn(_worker, args=(2, _free_port(), family, ret), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, _free_port(), family, fused, ret), nprocs=2, join=True)
     assert ret[0]["worst"] <= LOGIT_TOL, ret[0]["worst"]
     assert ret[0]["tokens"] == ret[1]["tokens"]              # replicated sampling agrees across ranks
     assert ret[0]["tokens2"] == ret[0]["tokens"]             # graph replay + prefix cache: same stream
@@ -95,4 +98,4 @@ def test_tp2_matches_oracle_and_tp1(family):
         while common < min(len(a), len(b)) and a[common] == b[common]:
             common += 1
         assert common >= min(len(a), len(b)) // 2, (a, b)
-    print(f"{family}: TP=2 worst |dlogit| {ret[0]['worst']:.4f}")
+    print(f"{family} fused={fused}: TP=2 worst |dlogit| {ret[0]['worst']:.4f}")
