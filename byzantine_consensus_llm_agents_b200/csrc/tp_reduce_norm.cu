@@ -91,20 +91,27 @@ tp_add_rmsnorm_kernel(float* __restrict__ residual, void* const* __restrict__ pe
     if (v < nvec) {
       float4 r = *reinterpret_cast<const float4*>(residual + static_cast<long long>(t) * d + v * 4);
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int rk = 0; rk < size; ++rk) {   // fixed (rank, split) order on every rank
-        const float* base = reinterpret_cast<const float*>(peers[rk]) + region_offset +
-                            static_cast<long long>(t) * d + v * 4;
-        for (int s0 = 0; s0 < n_partials; s0 += 4) {
-          float4 p[4];
+      // all (rank, split) slabs as one flat list, loaded eight at a time so that a whole batch
+      // of peer reads shares one NVLink round trip; summed in list order = fixed (rank, split)
+      // order on every rank
+      const int total = size * n_partials;
+      const long long elem = static_cast<long long>(t) * d + v * 4;
+      for (int i0 = 0; i0 < total; i0 += 8) {
+        float4 p[8];
 #pragma unroll
-          for (int s = 0; s < 4; ++s)
-            if (s0 + s < n_partials) p[s] = ld_peer_v4(base + (s0 + s) * partial_stride);
-#pragma unroll
-          for (int s = 0; s < 4; ++s)
-            if (s0 + s < n_partials) {
-              acc.x += p[s].x; acc.y += p[s].y; acc.z += p[s].z; acc.w += p[s].w;
-            }
+        for (int k = 0; k < 8; ++k) {
+          const int idx = i0 + k;
+          if (idx < total) {
+            const int rk = idx / n_partials, sp = idx - rk * n_partials;
+            p[k] = ld_peer_v4(reinterpret_cast<const float*>(peers[rk]) + region_offset + elem +
+                              sp * partial_stride);
+          }
         }
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          if (i0 + k < total) {
+            acc.x += p[k].x; acc.y += p[k].y; acc.z += p[k].z; acc.w += p[k].w;
+          }
       }
       r.x += acc.x; r.y += acc.y; r.z += acc.z; r.w += acc.w;
       x[i] = r;
