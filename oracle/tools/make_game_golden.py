@@ -24,7 +24,8 @@ from oracle import ref_harness as H
 from oracle.engine import OracleEngine
 from oracle.model import build_hf_model
 
-HF_NAME = {"qwen3-0.6b": "Qwen/Qwen3-0.6B", "qwen3-8b": "Qwen/Qwen3-8B", "qwen3-14b": "Qwen/Qwen3-14B"}
+HF_NAME = {"qwen3-0.6b": "Qwen/Qwen3-0.6B", "qwen3-8b": "Qwen/Qwen3-8B", "qwen3-14b": "Qwen/Qwen3-14B",
+           "mistral-22b": "mistralai/Mistral-Small-Instruct-2409"}
 
 
 def main():
