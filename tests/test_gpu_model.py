@@ -178,3 +178,20 @@ def test_qwen3_0p6b_full_depth_logits():
     # outlier beyond 2.5e-2.
     assert over <= 1e-5 * count, f"{over} of {count} logits differ by more than {LOGIT_TOL}"
     assert worst <= 2.5e-2
+
+
+def test_waves_and_prefill_groups_do_not_change_results():
+    """More rows than the engine's batch (-> several waves) and more new tokens than the prefill
+    workspace (-> several prefill groups inside a wave) must give what one-row calls give."""
+    hf, eng, tk = _setup(TINY_QWEN, enable_prefix_cache=False)       # max_rows 8, prefill workspace 2048
+    rng = np.random.default_rng(7)
+    lens = [700, 650, 500, 400, 300, 90, 60, 33, 20, 10, 5]          # 11 rows, 2768 prompt tokens
+    prompts = _prompts(tk, rng, lens)
+    schema = {"type": "object", "properties": {"decision": {"type": "string", "enum": ["stop", "continue"]}},
+              "required": ["decision"], "additionalProperties": False}
+    together = eng.generate([Request("", schema, 0.0, 16, prompt_ids=p) for p in prompts])
+    assert len(together) == len(prompts)
+    for i in (0, 3, 8, 10):
+        alone = eng.generate([Request("", schema, 0.0, 16, prompt_ids=prompts[i])])[0]
+        assert alone.token_ids == together[i].token_ids, i
+    assert all(r.prompt_tokens == n for r, n in zip(together, lens))
