@@ -211,6 +211,11 @@ def cpu_baseline(model_key: str, rounds, n_agents: int, layers_sample: int = 2, 
     full = PRESETS[model_key]
     cfg = ModelConfig(**{**full.__dict__, "n_layers": layers_sample, "name": full.name + "-sample"})
     tk = get_tokenizer(cfg.family, cfg.vocab)
+    # torchrun exports OMP_NUM_THREADS=1; the CPU arm is meant to use every host core
+    try:
+        torch.set_num_threads(os.cpu_count() or 1)
+    except Exception:
+        pass
     threads = torch.get_num_threads()
     hf = build_hf_model(cfg, seed=0)
     eng = OracleEngine(hf, tk, base_seed=0, memoise=False)
