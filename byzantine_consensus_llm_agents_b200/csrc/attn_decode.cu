@@ -186,11 +186,13 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
       }
       // ---- online softmax of row g over this page's 16 tokens (this lane: tokens vt[0..3])
       const int base_tok = tok0 + p * kPage;
+      // only a row's last page can hold tokens past its length (warp-uniform test)
+      const bool ragged = base_tok + kPage > tok1;
       float sv4[4];
       bool ok[4];
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        ok[i] = base_tok + vt[i] < tok1;
+        ok[i] = !ragged || base_tok + vt[i] < tok1;
         sv4[i] = ok[i] ? s[i >> 1][i & 1] * scale_log2e : -INFINITY;
       }
       float mx = fmaxf(fmaxf(sv4[0], sv4[1]), fmaxf(sv4[2], sv4[3]));
@@ -206,21 +208,32 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
       l_run = l_run * corr + (pr[0] + pr[1]) + (pr[2] + pr[3]);
       const uint32_t pa0 = pack_bf16(pr[0], pr[1]);
       const uint32_t pa2 = pack_bf16(pr[2], pr[3]);
-      // ---- O = O * corr + P V
+      // ---- O = O * corr + P V   (corr is exactly 1 whenever no row's running maximum moved:
+      // skipping the multiply then changes nothing, and most pages after the first few qualify)
+      const bool rescale = __any_sync(0xffffffffu, corr != 1.f);
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         uint4 vf[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           vf[i] = lds_v4(sv + h * 2048 + vt[i] * 128 + ((g ^ (vt[i] & 7)) << 4));
+        }
+        if (ragged) {
           // never multiply stale cache contents (possibly non-finite) by p = 0
-          if (!ok[i]) vf[i] = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            if (!ok[i]) vf[i] = make_uint4(0u, 0u, 0u, 0u);
+        }
+        if (rescale) {
+#pragma unroll
+          for (int jj = 0; jj < 8; ++jj) {
+            o[h * 8 + jj][0] *= corr;
+            o[h * 8 + jj][1] *= corr;
+          }
         }
 #pragma unroll
         for (int jj = 0; jj < 8; ++jj) {
           const int j = h * 8 + jj;
-          o[j][0] *= corr;
-          o[j][1] *= corr;
           const int w = jj >> 1;
           const uint32_t sel = (jj & 1) ? 0x7632u : 0x5410u;
           const uint32_t* v0 = reinterpret_cast<const uint32_t*>(&vf[0]);
@@ -251,78 +264,136 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
     }
   }
   __syncthreads();
+  // ---- the CTA's two warps -> one (m, l, o[128]) per head for this chunk.  A thread owns
+  // 4 consecutive dims of one head ("quad"): G * 32 quads over 96 threads.
   const int tid = threadIdx.x;
-  for (int d = tid; d < 128; d += kAttnThreads) {
+  constexpr int kQuads = G * 32;
+  const bool single = (n_splits == 1);  // short row: this chunk IS the result, no scratch round trip
+  for (int qd = tid; qd < kQuads; qd += kAttnThreads) {
+    const int gg = qd >> 5, d = (qd & 31) * 4;
+    float mm = -INFINITY;
 #pragma unroll
-    for (int gg = 0; gg < G; ++gg) {
-      float mm = -INFINITY;
+    for (int w = 0; w < kAttnConsumers; ++w) mm = fmaxf(mm, sm_m[w][gg]);
+    const float mu = (mm == -INFINITY) ? 0.f : mm;
+    float4 oo = make_float4(0.f, 0.f, 0.f, 0.f);
+    float ll = 0.f;
 #pragma unroll
-      for (int w = 0; w < kAttnConsumers; ++w) mm = fmaxf(mm, sm_m[w][gg]);
-      const float mu = (mm == -INFINITY) ? 0.f : mm;
-      float oo = 0.f, ll = 0.f;
-#pragma unroll
-      for (int w = 0; w < kAttnConsumers; ++w) {
-        const float c = exp2f(sm_m[w][gg] - mu);  // a warp without pages has m = -inf -> weight 0
-        oo += sm_acc[w][gg][d] * c;
-        ll += sm_l[w][gg] * c;
-      }
+    for (int w = 0; w < kAttnConsumers; ++w) {
+      const float c = exp2f(sm_m[w][gg] - mu);  // a warp without pages has m = -inf -> weight 0
+      const float4 a = *reinterpret_cast<const float4*>(&sm_acc[w][gg][d]);
+      oo.x += a.x * c; oo.y += a.y * c; oo.z += a.z * c; oo.w += a.w * c;
+      ll += sm_l[w][gg] * c;
+    }
+    if (single) {
+      // identical to merging one chunk: its weight is exp2(m - m) = 1
+      __nv_bfloat16* dst = out + (static_cast<long long>(b) * n_heads + head0 + gg) * 128 + d;
+      const bool nz = ll > 0.f;
+      uint2 pk;
+      pk.x = pack_bf16(nz ? oo.x / ll : 0.f, nz ? oo.y / ll : 0.f);
+      pk.y = pack_bf16(nz ? oo.z / ll : 0.f, nz ? oo.w / ll : 0.f);
+      *reinterpret_cast<uint2*>(dst) = pk;
+    } else {
       const long long idx = (static_cast<long long>(b) * n_heads + head0 + gg) * max_splits + split;
-      scratch_o[idx * 128 + d] = oo;
-      if (d == 0) {
-        scratch_ml[idx * 2] = mm;
-        scratch_ml[idx * 2 + 1] = ll;
-      }
+      *reinterpret_cast<float4*>(&scratch_o[idx * 128 + d]) = oo;
+      if (d == 0) *reinterpret_cast<float2*>(&scratch_ml[idx * 2]) = make_float2(mm, ll);
     }
   }
+  if (single) return;
   // ---- the chunk that finishes last merges all chunks of this (row, KV head), always in chunk
-  // order, so the result does not depend on which CTA happens to be last
-  __threadfence();
+  // order, so the result does not depend on which CTA happens to be last.  Release/acquire runs
+  // through one thread: the CTA barrier orders every thread's partial-result stores before
+  // thread 0's fence + counter increment, and thread 0's fence after the increment orders the
+  // other chunks' stores before the loads that follow the second barrier (which read L2).
   __syncthreads();
   if (tid == 0) {
+    fence_acq_rel_gpu();
     const int prev = atomicAdd(&counters[b * n_kv_heads + kvh], 1);
+    fence_acq_rel_gpu();
     sm_last = (prev == n_splits - 1);
   }
   __syncthreads();
-  if (sm_last) {
-    __threadfence();
-    for (int d = tid; d < 128; d += kAttnThreads)
+  if (!sm_last) return;
+  const long long base0 = (static_cast<long long>(b) * n_heads + head0) * max_splits;
+  if (n_splits <= 8) {
+    // every partial of a quad is requested before any is used: one L2 round trip per quad
+    for (int qd = tid; qd < kQuads; qd += kAttnThreads) {
+      const int gg = qd >> 5, d = (qd & 31) * 4;
+      const long long base = base0 + static_cast<long long>(gg) * max_splits;
+      float2 ml[8];
+      float4 ov[8];
 #pragma unroll
-    for (int gg = 0; gg < G; ++gg) {
-      const long long base = (static_cast<long long>(b) * n_heads + head0 + gg) * max_splits;
-      // loads are issued eight chunks at a time (independent), the arithmetic stays in chunk order
+      for (int k = 0; k < 8; ++k) {
+        const bool in = k < n_splits;
+        ml[k] = in ? __ldcg(reinterpret_cast<const float2*>(&scratch_ml[(base + k) * 2]))
+                   : make_float2(-INFINITY, 0.f);
+        ov[k] = in ? __ldcg(reinterpret_cast<const float4*>(&scratch_o[(base + k) * 128 + d]))
+                   : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      float mm = -INFINITY;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) mm = fmaxf(mm, ml[k].x);
+      const float mu = (mm == -INFINITY) ? 0.f : mm;
+      float4 oo = make_float4(0.f, 0.f, 0.f, 0.f);
+      float ll = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        if (k < n_splits) {
+          const float c = exp2f(ml[k].x - mu);
+          oo.x += ov[k].x * c; oo.y += ov[k].y * c; oo.z += ov[k].z * c; oo.w += ov[k].w * c;
+          ll += ml[k].y * c;
+        }
+      }
+      const bool nz = ll > 0.f;
+      uint2 pk;
+      pk.x = pack_bf16(nz ? oo.x / ll : 0.f, nz ? oo.y / ll : 0.f);
+      pk.y = pack_bf16(nz ? oo.z / ll : 0.f, nz ? oo.w / ll : 0.f);
+      *reinterpret_cast<uint2*>(out + (static_cast<long long>(b) * n_heads + head0 + gg) * 128 + d) = pk;
+    }
+  } else {
+    // long rows (> 2048 tokens): same arithmetic, chunks fetched eight at a time
+    for (int qd = tid; qd < kQuads; qd += kAttnThreads) {
+      const int gg = qd >> 5, d = (qd & 31) * 4;
+      const long long base = base0 + static_cast<long long>(gg) * max_splits;
       float mm = -INFINITY;
       for (int s0 = 0; s0 < n_splits; s0 += 8) {
         float mv[8];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) mv[k] = (s0 + k < n_splits) ? __ldcg(&scratch_ml[(base + s0 + k) * 2]) : -INFINITY;
+        for (int k = 0; k < 8; ++k)
+          mv[k] = (s0 + k < n_splits) ? __ldcg(&scratch_ml[(base + s0 + k) * 2]) : -INFINITY;
 #pragma unroll
         for (int k = 0; k < 8; ++k) mm = fmaxf(mm, mv[k]);
       }
       const float mu = (mm == -INFINITY) ? 0.f : mm;
-      float oo = 0.f, ll = 0.f;
+      float4 oo = make_float4(0.f, 0.f, 0.f, 0.f);
+      float ll = 0.f;
       for (int s0 = 0; s0 < n_splits; s0 += 8) {
-        float mv[8], lv[8], ov[8];
+        float2 ml[8];
+        float4 ov[8];
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           const bool in = s0 + k < n_splits;
-          mv[k] = in ? __ldcg(&scratch_ml[(base + s0 + k) * 2]) : -INFINITY;
-          lv[k] = in ? __ldcg(&scratch_ml[(base + s0 + k) * 2 + 1]) : 0.f;
-          ov[k] = in ? __ldcg(&scratch_o[(base + s0 + k) * 128 + d]) : 0.f;
+          ml[k] = in ? __ldcg(reinterpret_cast<const float2*>(&scratch_ml[(base + s0 + k) * 2]))
+                     : make_float2(-INFINITY, 0.f);
+          ov[k] = in ? __ldcg(reinterpret_cast<const float4*>(&scratch_o[(base + s0 + k) * 128 + d]))
+                     : make_float4(0.f, 0.f, 0.f, 0.f);
         }
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           if (s0 + k < n_splits) {
-            const float c = exp2f(mv[k] - mu);
-            oo += ov[k] * c;
-            ll += lv[k] * c;
+            const float c = exp2f(ml[k].x - mu);
+            oo.x += ov[k].x * c; oo.y += ov[k].y * c; oo.z += ov[k].z * c; oo.w += ov[k].w * c;
+            ll += ml[k].y * c;
           }
         }
       }
-      out[(static_cast<long long>(b) * n_heads + head0 + gg) * 128 + d] =
-          __float2bfloat16_rn(ll > 0.f ? oo / ll : 0.f);
+      const bool nz = ll > 0.f;
+      uint2 pk;
+      pk.x = pack_bf16(nz ? oo.x / ll : 0.f, nz ? oo.y / ll : 0.f);
+      pk.y = pack_bf16(nz ? oo.z / ll : 0.f, nz ? oo.w / ll : 0.f);
+      *reinterpret_cast<uint2*>(out + (static_cast<long long>(b) * n_heads + head0 + gg) * 128 + d) = pk;
     }
-    if (tid == 0) counters[b * n_kv_heads + kvh] = 0;  // leave the counters zero for the next call
   }
+  if (tid == 0) counters[b * n_kv_heads + kvh] = 0;  // leave the counters zero for the next call
 }
 
 template <int G>
@@ -364,6 +435,11 @@ int decode_attn_paged(const void* q, const void* kv_cache, const int* block_tabl
   if (page_size != kPage) {
     set_last_error("bcg_decode_attn_paged", "page_size must be 16");
     return BCG_ERR_UNSUPPORTED;
+  }
+  if ((reinterpret_cast<uintptr_t>(scratch_o) & 15) || (reinterpret_cast<uintptr_t>(scratch_ml) & 7) ||
+      (reinterpret_cast<uintptr_t>(out) & 7)) {
+    set_last_error("bcg_decode_attn_paged", "scratch_o must be 16-byte, scratch_ml and out 8-byte aligned");
+    return BCG_ERR_ARG;
   }
   const int G = n_heads / n_kv_heads;
   int rc;

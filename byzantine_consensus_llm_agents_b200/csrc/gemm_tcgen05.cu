@@ -28,6 +28,8 @@ constexpr int kBlockK = 64;
 constexpr int kUmmaK = 16;
 constexpr int kGemmThreads = 192;
 
+constexpr int kPreWaitStages = 6;  // weight slots requested before griddepcontrol.wait
+
 struct GemmArgs {
   int M, N, K;              // logical problem
   int tiles_a, tiles_b;     // tiles along the A-operand rows / B-operand rows
@@ -39,7 +41,7 @@ struct GemmArgs {
   void* out;
   long long ld_out;         // elements
   uint64_t hint_a, hint_b;
-  int pdl_wait_b;           // 1: only the B-operand (activations) depends on the previous kernel
+  int pdl_wait_b;           // 1: launched with programmatic stream serialization (see the producer)
 };
 
 __device__ __forceinline__ float silu_mul(float g, float u) {
@@ -111,21 +113,43 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   if (warp == 0) {
     // ------------------------------ TMA producer ------------------------------
     if (lane == 0) {
+      // Under programmatic dependent launch this CTA may start while the previous kernel is still
+      // running.  Weights never depend on it, activations do: so the weight halves of the first
+      // kPreWaitStages ring slots are requested right away and only then does the producer wait
+      // for the previous kernel and add the activation halves.  (Measured on the 14B decode step:
+      // 1 slot 6.24 ms, 4 slots 6.15, 6 slots 5.97, all 10 slots 6.03 — deeper prefetch starts
+      // to take bandwidth from the predecessor; pulling further tiles into L2 with
+      // cp.async.bulk.prefetch made the step monotonically slower, 6.16 -> 6.93 ms at 64 tiles.)
+      int n_pre = 0;
+      if (args.pdl_wait_b) {
+        if (args.swap) {
+          constexpr int pre = STAGES < kPreWaitStages ? STAGES : kPreWaitStages;
+          int idx = 0;
+          for (int item = blockIdx.x; item < total_items && idx < pre; item += gridDim.x) {
+            int ta, tb, split, kb0, kb1;
+            decode_item(item, ta, tb, split, kb0, kb1);
+            for (int kb = kb0; kb < kb1 && idx < pre; ++kb, ++idx) {
+              mbar_arrive_expect_tx(&full_bar[idx], STAGE_BYTES);
+              tma_load_2d(smem + idx * STAGE_BYTES, &tmap_a, &full_bar[idx], kb * kBlockK,
+                          ta * kBlockA, args.hint_a);
+              n_pre = idx + 1;
+            }
+          }
+        }
+        pdl_wait();
+      }
       int stage = 0;
       uint32_t phase = 0;
-      bool waited = (args.pdl_wait_b == 0);
+      int idx = 0;
       for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
         int ta, tb, split, kb0, kb1;
         decode_item(item, ta, tb, split, kb0, kb1);
-        for (int kb = kb0; kb < kb1; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
+        for (int kb = kb0; kb < kb1; ++kb, ++idx) {
           uint8_t* sa = smem + stage * STAGE_BYTES;
-          mbar_arrive_expect_tx(&full_bar[stage], STAGE_BYTES);
-          tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kBlockK, ta * kBlockA, args.hint_a);
-          if (!waited) {
-            // weights never depend on the previous kernel; activations do.
-            pdl_wait();
-            waited = true;
+          if (idx >= n_pre) {
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            mbar_arrive_expect_tx(&full_bar[stage], STAGE_BYTES);
+            tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kBlockK, ta * kBlockA, args.hint_a);
           }
           tma_load_2d(sa + A_BYTES, &tmap_b, &full_bar[stage], kb * kBlockK, tb * BN,
                       args.hint_b);

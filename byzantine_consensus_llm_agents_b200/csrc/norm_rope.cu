@@ -9,6 +9,8 @@
 // oracle); every row is computed independently of the batch it is in (batch-invariant).
 // Arithmetic follows transformers' Qwen3RMSNorm / apply_rotary_pos_emb in fp32
 // (modeling_qwen3.py:50-64,86-148 as cited in SURVEY.md §8c).
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -73,71 +75,196 @@ embed_rmsnorm_kernel(const int* __restrict__ ids, const __nv_bfloat16* __restric
   }
 }
 
+// ---------------------------------------------------------------------------------------
+// add_rmsnorm.  Decode calls this twice per layer on <= 128 rows: one CTA per row leaves 138 SMs
+// idle and makes every thread walk ~60 values through several dependent L2 round trips, so the
+// kernel was pure latency (5.4 us against 0.4 us of traffic).  A row is therefore cut into
+// kNormSegments segments of "virtual threads":
+//     vector v (4 floats)  ->  segment s = v / per,  j = v - s * per   (per = ceil(nvec / 8))
+//                              virtual thread vt = j % 256,  turn i = j / 256
+// and the sum of squares is ALWAYS formed in this one order: virtual thread (turns in order)
+// -> xor-shuffle tree over its 32-lane virtual warp -> the segment's 8 warps in order -> the
+// 8 segments in order.  Two kernels execute that order:
+//   * add_rmsnorm_cluster_kernel (T <= 128): a cluster of 8 CTAs x 256 threads per row, one
+//     segment per CTA, every load of a thread in flight at once, segment sums exchanged through
+//     distributed shared memory;
+//   * add_rmsnorm_row_kernel (prefill-sized T): one 1024-thread CTA per row, whose 32 warps play
+//     the 64 virtual warps in two turns.
+// Same order, same intrinsics -> bit-identical rows, so a row's result does not depend on how
+// many other rows share the launch (batch invariance across prefill and decode shapes).
+//
 // src_rows == nullptr: in-place residual update over all T rows.
 // src_rows != nullptr: row i reads residual/delta row src_rows[i], writes xn row i only
 //                      (last-token gather in front of lm_head); residual is left untouched.
+// ---------------------------------------------------------------------------------------
+constexpr int kNormSegments = 8;
+constexpr int kSegThreads = 256;
+constexpr int kSegTurns = 2;  // d <= 8 * 256 * 2 * 4 = 16384
+constexpr int kPartialsInFlight = 16;
+constexpr int kNormClusterMaxRows = 128;  // decode-sized launches take the cluster kernel
+
+__device__ __forceinline__ float sumsq4(const float4& x) {
+  return __fmaf_rn(x.w, x.w, __fmaf_rn(x.z, x.z, __fmaf_rn(x.y, x.y, __fmul_rn(x.x, x.x))));
+}
+
+// residual row + delta (bf16, or fp32 split-K partials added in index order) for one vector.
+// BATCH partial loads are issued before any is used.
+template <int BATCH>
+__device__ __forceinline__ float4 residual_plus_delta(const float* __restrict__ residual,
+                                                      const void* __restrict__ delta,
+                                                      int delta_is_f32, int n_partials,
+                                                      long long partial_stride, long long off) {
+  float4 r = *reinterpret_cast<const float4*>(residual + off);
+  if (!delta) return r;
+  if (!delta_is_f32) {
+    const uint2 raw = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(delta) + off);
+    r.x += bf16lo(raw.x); r.y += bf16hi(raw.x); r.z += bf16lo(raw.y); r.w += bf16hi(raw.y);
+    return r;
+  }
+  const float* dp = reinterpret_cast<const float*>(delta) + off;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int s0 = 0; s0 < n_partials; s0 += BATCH) {
+    float4 p[BATCH];
+#pragma unroll
+    for (int s = 0; s < BATCH; ++s)
+      if (s0 + s < n_partials) p[s] = *reinterpret_cast<const float4*>(dp + (s0 + s) * partial_stride);
+#pragma unroll
+    for (int s = 0; s < BATCH; ++s) {
+      if (s0 + s < n_partials) {
+        if (s0 + s == 0) {
+          acc = p[s];
+        } else {
+          acc.x += p[s].x; acc.y += p[s].y; acc.z += p[s].z; acc.w += p[s].w;
+        }
+      }
+    }
+  }
+  r.x += acc.x; r.y += acc.y; r.z += acc.z; r.w += acc.w;
+  return r;
+}
+
+__device__ __forceinline__ void norm_store(float* __restrict__ residual, __nv_bfloat16* __restrict__ xn,
+                                           bool write_residual, long long off, const float4& x,
+                                           const float4& ww, float inv) {
+  if (write_residual) *reinterpret_cast<float4*>(residual + off) = x;
+  store_bf16x4(xn + off, x.x * inv * ww.x, x.y * inv * ww.y, x.z * inv * ww.z, x.w * inv * ww.w);
+}
+
+__global__ void __cluster_dims__(kNormSegments, 1, 1) __launch_bounds__(kSegThreads)
+add_rmsnorm_cluster_kernel(float* __restrict__ residual, const void* __restrict__ delta,
+                           int delta_is_f32, int n_partials, long long partial_stride,
+                           const float* __restrict__ w, __nv_bfloat16* __restrict__ xn,
+                           const int* __restrict__ src_rows, int d, float eps) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  __shared__ float red[kSegThreads / 32];
+  __shared__ float seg_ss;                 // this segment's sum of squares (read by the peers)
+  __shared__ float all_ss[kNormSegments];
+  pdl_launch_dependents();
+  pdl_wait();
+  const int seg = blockIdx.x;  // == rank in the cluster
+  const int t = blockIdx.y;
+  const long long src = src_rows ? src_rows[t] : t;
+  const int nvec = d >> 2;
+  const int per = (nvec + kNormSegments - 1) / kNormSegments;
+  const int v_end = min(nvec, (seg + 1) * per);
+  float4 x[kSegTurns], ww[kSegTurns];
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < kSegTurns; ++i) {
+    const int v = seg * per + threadIdx.x + i * kSegThreads;
+    if (threadIdx.x + i * kSegThreads < per && v < v_end) {
+      ww[i] = *reinterpret_cast<const float4*>(w + v * 4);
+      x[i] = residual_plus_delta<kPartialsInFlight>(residual, delta, delta_is_f32, n_partials,
+                                                    partial_stride, src * d + v * 4);
+      ss = __fadd_rn(ss, sumsq4(x[i]));
+    }
+  }
+  ss = warp_sum(ss);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float sg = 0.f;
+#pragma unroll
+    for (int i = 0; i < kSegThreads / 32; ++i) sg += red[i];
+    seg_ss = sg;
+  }
+  cluster.sync();
+  if (threadIdx.x < kNormSegments) all_ss[threadIdx.x] = *cluster.map_shared_rank(&seg_ss, threadIdx.x);
+  __syncthreads();
+  cluster.barrier_arrive();  // my reads of the peers' seg_ss are done
+  float tot = 0.f;
+#pragma unroll
+  for (int i = 0; i < kNormSegments; ++i) tot += all_ss[i];
+  const float inv = rsqrtf(tot / static_cast<float>(d) + eps);
+#pragma unroll
+  for (int i = 0; i < kSegTurns; ++i) {
+    const int v = seg * per + threadIdx.x + i * kSegThreads;
+    if (threadIdx.x + i * kSegThreads < per && v < v_end)
+      norm_store(residual, xn, !src_rows, static_cast<long long>(t) * d + v * 4, x[i], ww[i], inv);
+  }
+  cluster.barrier_wait();  // nobody leaves while a peer may still read its seg_ss
+}
+
+// One CTA per row; physical warp pw plays virtual warps pw and pw + 32 (see the order above).
 __global__ void __launch_bounds__(kNormThreads)
-add_rmsnorm_kernel(float* __restrict__ residual, const void* __restrict__ delta, int delta_is_f32,
-                   int n_partials, long long partial_stride, const float* __restrict__ w,
-                   __nv_bfloat16* __restrict__ xn, const int* __restrict__ src_rows, int d,
-                   float eps) {
-  __shared__ float red[kNormThreads / 32];
+add_rmsnorm_row_kernel(float* __restrict__ residual, const void* __restrict__ delta, int delta_is_f32,
+                       int n_partials, long long partial_stride, const float* __restrict__ w,
+                       __nv_bfloat16* __restrict__ xn, const int* __restrict__ src_rows, int d,
+                       float eps) {
+  constexpr int kVirtWarps = kNormSegments * kSegThreads / 32;  // 64
+  constexpr int kRounds = kVirtWarps / (kNormThreads / 32);     // 2
+  __shared__ float red[kVirtWarps];
   pdl_launch_dependents();
   pdl_wait();
   const int t = blockIdx.x;
   const long long src = src_rows ? src_rows[t] : t;
   const int nvec = d >> 2;
-  float4 x[kMaxVecPerThread];
-  float ss = 0.f;
+  const int per = (nvec + kNormSegments - 1) / kNormSegments;
+  const int pw = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float4 x[kRounds][kSegTurns];
 #pragma unroll
-  for (int i = 0; i < kMaxVecPerThread; ++i) {
-    const int v = threadIdx.x + i * kNormThreads;
-    if (v < nvec) {
-      float4 r = *reinterpret_cast<const float4*>(residual + src * d + v * 4);
-      if (delta) {
-        if (delta_is_f32) {
-          const float* dp = reinterpret_cast<const float*>(delta) + src * d + v * 4;
-          // issue all partial loads first (independent, up to 8 in flight), then add them in
-          // index order: same arithmetic as a serial loop, a fraction of its latency
-          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-          for (int s0 = 0; s0 < n_partials; s0 += kMaxPartialsBatch) {
-            float4 p[kMaxPartialsBatch];
+  for (int r = 0; r < kRounds; ++r) {
+    const int vw = pw + r * (kNormThreads / 32);
+    const int seg = vw >> 3;
+    const int vt = (vw & 7) * 32 + lane;
+    const int v_end = min(nvec, (seg + 1) * per);
+    float ss = 0.f;
 #pragma unroll
-            for (int s = 0; s < kMaxPartialsBatch; ++s) {
-              if (s0 + s < n_partials) p[s] = *reinterpret_cast<const float4*>(dp + (s0 + s) * partial_stride);
-            }
-#pragma unroll
-            for (int s = 0; s < kMaxPartialsBatch; ++s) {
-              if (s0 + s < n_partials) {
-                if (s0 + s == 0) {
-                  acc = p[s];
-                } else {
-                  acc.x += p[s].x; acc.y += p[s].y; acc.z += p[s].z; acc.w += p[s].w;
-                }
-              }
-            }
-          }
-          r.x += acc.x; r.y += acc.y; r.z += acc.z; r.w += acc.w;
-        } else {
-          const uint2 raw = *reinterpret_cast<const uint2*>(
-              reinterpret_cast<const __nv_bfloat16*>(delta) + src * d + v * 4);
-          r.x += bf16lo(raw.x); r.y += bf16hi(raw.x); r.z += bf16lo(raw.y); r.w += bf16hi(raw.y);
-        }
+    for (int i = 0; i < kSegTurns; ++i) {
+      const int v = seg * per + vt + i * kSegThreads;
+      if (vt + i * kSegThreads < per && v < v_end) {
+        x[r][i] = residual_plus_delta<kMaxPartialsBatch>(residual, delta, delta_is_f32, n_partials,
+                                                         partial_stride, src * d + v * 4);
+        ss = __fadd_rn(ss, sumsq4(x[r][i]));
       }
-      x[i] = r;
-      ss += r.x * r.x + r.y * r.y + r.z * r.z + r.w * r.w;
     }
+    ss = warp_sum(ss);
+    if (lane == 0) red[vw] = ss;
   }
-  const float tot = block_sum(ss, red);
+  __syncthreads();
+  float tot = 0.f;
+#pragma unroll
+  for (int sgi = 0; sgi < kNormSegments; ++sgi) {
+    float sg = 0.f;
+#pragma unroll
+    for (int i = 0; i < kSegThreads / 32; ++i) sg += red[sgi * (kSegThreads / 32) + i];
+    tot += sg;
+  }
   const float inv = rsqrtf(tot / static_cast<float>(d) + eps);
 #pragma unroll
-  for (int i = 0; i < kMaxVecPerThread; ++i) {
-    const int v = threadIdx.x + i * kNormThreads;
-    if (v < nvec) {
-      if (!src_rows) *reinterpret_cast<float4*>(residual + static_cast<long long>(t) * d + v * 4) = x[i];
-      const float4 ww = *reinterpret_cast<const float4*>(w + v * 4);
-      store_bf16x4(xn + static_cast<long long>(t) * d + v * 4, x[i].x * inv * ww.x,
-                   x[i].y * inv * ww.y, x[i].z * inv * ww.z, x[i].w * inv * ww.w);
+  for (int r = 0; r < kRounds; ++r) {
+    const int vw = pw + r * (kNormThreads / 32);
+    const int seg = vw >> 3;
+    const int vt = (vw & 7) * 32 + lane;
+    const int v_end = min(nvec, (seg + 1) * per);
+#pragma unroll
+    for (int i = 0; i < kSegTurns; ++i) {
+      const int v = seg * per + vt + i * kSegThreads;
+      if (vt + i * kSegThreads < per && v < v_end) {
+        const float4 ww = *reinterpret_cast<const float4*>(w + v * 4);
+        norm_store(residual, xn, !src_rows, static_cast<long long>(t) * d + v * 4, x[r][i], ww, inv);
+      }
     }
   }
 }
@@ -259,13 +386,19 @@ int add_rmsnorm(float* residual, const void* delta, int delta_is_f32, int n_part
                 long long partial_stride, const float* w, void* xn, const int* src_rows, int T,
                 int d, float eps, cudaStream_t stream) {
   if (!residual || !w || !xn || T <= 0 || d <= 0 || (d % 4) ||
-      d > kNormThreads * kMaxVecPerThread * 4 || n_partials < 1) {
-    set_last_error("bcg_add_rmsnorm", "bad argument (d must be a multiple of 4 and <= 8192)");
+      d > kNormSegments * kSegThreads * kSegTurns * 4 || n_partials < 1) {
+    set_last_error("bcg_add_rmsnorm", "bad argument (d must be a multiple of 4 and <= 16384)");
     return BCG_ERR_ARG;
   }
-  BCG_CUDA_CHECK(launch_k(add_rmsnorm_kernel, dim3(T), dim3(kNormThreads), 0, stream, residual, delta,
-                          delta_is_f32, n_partials, partial_stride, w,
-                          reinterpret_cast<__nv_bfloat16*>(xn), src_rows, d, eps));
+  if (T <= kNormClusterMaxRows) {
+    BCG_CUDA_CHECK(launch_k(add_rmsnorm_cluster_kernel, dim3(kNormSegments, T), dim3(kSegThreads), 0,
+                            stream, residual, delta, delta_is_f32, n_partials, partial_stride, w,
+                            reinterpret_cast<__nv_bfloat16*>(xn), src_rows, d, eps));
+  } else {
+    BCG_CUDA_CHECK(launch_k(add_rmsnorm_row_kernel, dim3(T), dim3(kNormThreads), 0, stream, residual,
+                            delta, delta_is_f32, n_partials, partial_stride, w,
+                            reinterpret_cast<__nv_bfloat16*>(xn), src_rows, d, eps));
+  }
   return BCG_OK;
 }
 

@@ -164,7 +164,9 @@ def test_embed_rmsnorm(T, d):
     assert ((xn.float() - ref).abs() <= ref.abs() * 2 ** -7 + 1e-5).all()
 
 
-@pytest.mark.parametrize("T,d,parts", [(10, 1024, 0), (10, 5120, 4), (33, 2048, 1), (3, 8192, 7)])
+@pytest.mark.parametrize("T,d,parts", [(10, 1024, 0), (10, 5120, 4), (33, 2048, 1), (3, 8192, 7),
+                                       (200, 5120, 11), (129, 1024, 0), (7, 6144, 17), (5, 1000, 3),
+                                       (300, 16384, 2), (2, 16384, 5), (1, 256, 1)])
 def test_add_rmsnorm(T, d, parts):
     lib = _lib()
     res0 = torch.randn(T, d, device=DEV)
@@ -188,6 +190,31 @@ def test_add_rmsnorm(T, d, parts):
     assert torch.equal(res, ref_res)  # same fp32 operation order
     ref = _rmsnorm_ref(ref_res, w, 1e-6)
     assert ((xn.float() - ref).abs() <= ref.abs() * 2 ** -7 + 1e-5).all()
+
+
+@pytest.mark.parametrize("d,parts", [(5120, 11), (1024, 0), (1000, 3), (12288, 2)])
+def test_add_rmsnorm_row_is_independent_of_launch_size(d, parts):
+    """Decode-sized launches (<= 128 rows: one 8-CTA cluster per row) and prefill-sized ones (one CTA
+    per row) form the sum of squares in the same order: a row's xn is bit-identical either way."""
+    lib = _lib()
+    few, many = 6, 200
+    res_m = torch.randn(many, d, device=DEV)
+    w = (torch.rand(d, device=DEV) + 0.5).float()
+    if parts == 0:
+        delta_m = _rand_bf16(many, d, seed=21)
+    else:
+        delta_m = torch.randn(parts, many, d, device=DEV)
+    pick = [0, 57, 128, 199, 3, 77]
+    res_f = res_m[pick].clone()
+    delta_f = delta_m[pick].clone() if parts == 0 else delta_m[:, pick].contiguous()
+    xn_m = torch.empty(many, d, device=DEV, dtype=torch.bfloat16)
+    xn_f = torch.empty(few, d, device=DEV, dtype=torch.bfloat16)
+    for res, delta, xn, T in ((res_m, delta_m, xn_m, many), (res_f, delta_f, xn_f, few)):
+        L.check(lib.bcg_add_rmsnorm(res.data_ptr(), delta.data_ptr(), 1 if parts else 0, max(parts, 1),
+                                    T * d, w.data_ptr(), xn.data_ptr(), None, T, d, 1e-6, L.stream_ptr()))
+    torch.cuda.synchronize()
+    assert torch.equal(res_m[pick], res_f)
+    assert torch.equal(xn_m[pick].view(torch.int16), xn_f.view(torch.int16))
 
 
 def test_add_rmsnorm_gather_rows():
