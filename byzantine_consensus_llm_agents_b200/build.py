@@ -18,6 +18,7 @@ PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 OUT = PKG / "_lib"
 LIB = OUT / "libbcg_b200.so"
+LIB_TIMELINE = OUT / "libbcg_b200_tl.so"
 
 SOURCES = [
     "capi.cu",
@@ -56,17 +57,17 @@ def _digest() -> str:
     return h.hexdigest()
 
 
-def build(force: bool = False, verbose: bool = False) -> Path:
+def _build(lib: Path, defines, tag: str, force: bool, verbose: bool) -> Path:
     OUT.mkdir(exist_ok=True)
-    stamp = OUT / "build.stamp"
-    digest = _digest()
-    if not force and LIB.exists() and stamp.exists() and stamp.read_text().strip() == digest:
-        return LIB
+    stamp = OUT / f"build{tag}.stamp"
+    digest = _digest() + " ".join(defines)
+    if not force and lib.exists() and stamp.exists() and stamp.read_text().strip() == digest:
+        return lib
     nvcc = _nvcc()
-    extra = ["-Xptxas", "-v"] if verbose else []
+    extra = (["-Xptxas", "-v"] if verbose else []) + list(defines)
 
     def compile_one(src: str) -> Path:
-        obj = OUT / (src + ".o")
+        obj = OUT / (src + tag + ".o")
         cmd = [nvcc, *NVCC_FLAGS, *extra, "-c", str(CSRC / src), "-o", str(obj)]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if verbose or r.returncode != 0:
@@ -77,14 +78,25 @@ def build(force: bool = False, verbose: bool = False) -> Path:
 
     with ThreadPoolExecutor(max_workers=min(8, len(SOURCES))) as ex:
         objs = list(ex.map(compile_one, SOURCES))
-    cmd = [nvcc, "-shared", "-cudart", "static", "-o", str(LIB), *map(str, objs), "-ldl"]
+    cmd = [nvcc, "-shared", "-cudart", "static", "-o", str(lib), *map(str, objs), "-ldl"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)
         raise RuntimeError("link failed")
     stamp.write_text(digest)
-    return LIB
+    return lib
+
+
+def build(force: bool = False, verbose: bool = False) -> Path:
+    return _build(LIB, [], "", force, verbose)
+
+
+def build_timeline(force: bool = False, verbose: bool = False) -> Path:
+    """Dev-only variant with %globaltimer stamps compiled in (tools/timeline.py); never loaded
+    by the package itself."""
+    return _build(LIB_TIMELINE, ["-DBCG_TIMELINE"], ".tl", force, verbose)
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    fn = build_timeline if "--timeline" in sys.argv else build
+    print(fn(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -93,6 +93,7 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
   __shared__ float sm_l[kAttnConsumers][G];
   __shared__ int sm_last;
   pdl_launch_dependents();
+  if (threadIdx.x == 0) BCG_TL(4, 0);
 
   const int split = blockIdx.x;
   const int kvh = blockIdx.y;
@@ -107,18 +108,48 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
     }
     fence_barrier_init();
   }
-  pdl_wait();
-  // Requests that do not depend on the row's length go out together with the length itself:
-  // the producer's block-table entries (entries past the row's last page are unused) and the
-  // consumers' query fragments.  One memory round trip instead of two before the first TMA.
+  __syncthreads();
+  // ---- Before griddepcontrol.wait (i.e. possibly while the kernels in front of this one are
+  // still running) the CTA touches only data that no kernel of the running step writes: the
+  // row's length and block table (final before the step's first kernel starts: their writers —
+  // host copies and the sampler — never trigger dependents early) and KV pages other than the
+  // one that receives the row's newest token (written by qknorm_rope_kvwrite just in front of
+  // us).  So the producer fills the ring with old pages right away; only the queries and that
+  // last page wait for the predecessor.
   const int g = lane >> 2, t = lane & 3;
-  int my_phys = 0;
-  uint32_t qa[8][2];
-  if (warp == kAttnConsumers) {
+  const int seq_len = seq_lens[b];
+  const int n_splits = (seq_len + kSplitTokens - 1) / kSplitTokens;
+  const bool live = split < n_splits;
+  const int tok0 = split * kSplitTokens;
+  const int tok1 = min(seq_len, tok0 + kSplitTokens);
+  const int n_pages = live ? (tok1 - tok0 + kPage - 1) / kPage : 0;
+  auto issue_page = [&](int p, int phys) {
+    const int stage = p % kAttnStages;
+    uint8_t* dst = ring + stage * kAttnStageBytes;
+    const int row_k = ((phys * 2) * n_kv_heads + kvh) * kPage;
+    const int row_v = ((phys * 2 + 1) * n_kv_heads + kvh) * kPage;
+    mbar_arrive_expect_tx(&full_bar[stage], kAttnStageBytes);
+    tma_load_2d(dst, &kv_map, &full_bar[stage], 0, row_k, kEvictFirst);
+    tma_load_2d(dst + 2048, &kv_map, &full_bar[stage], 64, row_k, kEvictFirst);
+    tma_load_2d(dst + 4096, &kv_map, &full_bar[stage], 0, row_v, kEvictFirst);
+    tma_load_2d(dst + 6144, &kv_map, &full_bar[stage], 64, row_v, kEvictFirst);
+  };
+  int my_phys = 0, n_pre = 0;
+  if (live && warp == kAttnConsumers) {
     const int my_pg = split * (kSplitTokens / kPage) + lane;
     if (lane < kSplitTokens / kPage && my_pg < max_blocks)
       my_phys = block_table[static_cast<long long>(b) * max_blocks + my_pg];
-  } else {
+    n_pre = min(kAttnStages, n_pages - (split == n_splits - 1 ? 1 : 0));
+    for (int p = 0; p < n_pre; ++p) {
+      const int phys = __shfl_sync(0xffffffffu, my_phys, p);
+      if (lane == 0) issue_page(p, phys);
+    }
+  }
+  pdl_wait();
+  if (threadIdx.x == 0) BCG_TL(4, 1);
+  if (!live) return;  // whole CTA
+  uint32_t qa[8][2];
+  if (warp != kAttnConsumers) {
     // Q as A fragments: [k-step][a0 (k 2t,2t+1), a2 (k 8+2t,9+2t)]; rows 8..15 (a1, a3) are zero
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
@@ -131,29 +162,14 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
       qa[2 * j + 1][0] = raw.z; qa[2 * j + 1][1] = raw.w;
     }
   }
-  const int seq_len = seq_lens[b];
-  const int n_splits = (seq_len + kSplitTokens - 1) / kSplitTokens;
-  if (split >= n_splits) return;  // whole CTA
-  __syncthreads();
-  const int tok0 = split * kSplitTokens;
-  const int tok1 = min(seq_len, tok0 + kSplitTokens);
-  const int n_pages = (tok1 - tok0 + kPage - 1) / kPage;
 
   if (warp == kAttnConsumers) {
     // ------------------------------ TMA producer ------------------------------
-    for (int p = 0; p < n_pages; ++p) {
+    for (int p = n_pre; p < n_pages; ++p) {
       const int phys = __shfl_sync(0xffffffffu, my_phys, p);
       if (lane == 0) {
-        const int stage = p % kAttnStages;
-        if (p >= kAttnStages) mbar_wait(&empty_bar[stage], ((p / kAttnStages) - 1) & 1);
-        uint8_t* dst = ring + stage * kAttnStageBytes;
-        const int row_k = ((phys * 2) * n_kv_heads + kvh) * kPage;
-        const int row_v = ((phys * 2 + 1) * n_kv_heads + kvh) * kPage;
-        mbar_arrive_expect_tx(&full_bar[stage], kAttnStageBytes);
-        tma_load_2d(dst, &kv_map, &full_bar[stage], 0, row_k, kEvictFirst);
-        tma_load_2d(dst + 2048, &kv_map, &full_bar[stage], 64, row_k, kEvictFirst);
-        tma_load_2d(dst + 4096, &kv_map, &full_bar[stage], 0, row_v, kEvictFirst);
-        tma_load_2d(dst + 6144, &kv_map, &full_bar[stage], 64, row_v, kEvictFirst);
+        if (p >= kAttnStages) mbar_wait(&empty_bar[p % kAttnStages], ((p / kAttnStages) - 1) & 1);
+        issue_page(p, phys);
       }
     }
   } else {
@@ -264,6 +280,7 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
     }
   }
   __syncthreads();
+  if (threadIdx.x == 0) BCG_TL(4, 2);
   // ---- the CTA's two warps -> one (m, l, o[128]) per head for this chunk.  A thread owns
   // 4 consecutive dims of one head ("quad"): G * 32 quads over 96 threads.
   const int tid = threadIdx.x;
@@ -298,7 +315,10 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
       if (d == 0) *reinterpret_cast<float2*>(&scratch_ml[idx * 2]) = make_float2(mm, ll);
     }
   }
-  if (single) return;
+  if (single) {
+    if (threadIdx.x == 0) BCG_TL(4, 3);
+    return;
+  }
   // ---- the chunk that finishes last merges all chunks of this (row, KV head), always in chunk
   // order, so the result does not depend on which CTA happens to be last.  Release/acquire runs
   // through one thread: the CTA barrier orders every thread's partial-result stores before
@@ -312,7 +332,10 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
     sm_last = (prev == n_splits - 1);
   }
   __syncthreads();
-  if (!sm_last) return;
+  if (!sm_last) {
+    if (threadIdx.x == 0) BCG_TL(4, 3);
+    return;
+  }
   const long long base0 = (static_cast<long long>(b) * n_heads + head0) * max_splits;
   if (n_splits <= 8) {
     // every partial of a quad is requested before any is used: one L2 round trip per quad
@@ -321,17 +344,17 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
       const long long base = base0 + static_cast<long long>(gg) * max_splits;
       float2 ml[8];
       float4 ov[8];
+      // unconditional loads (chunks past the end re-read the last one and are ignored below), so
+      // that no load waits behind a predicate or an add
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
-        const bool in = k < n_splits;
-        ml[k] = in ? __ldcg(reinterpret_cast<const float2*>(&scratch_ml[(base + k) * 2]))
-                   : make_float2(-INFINITY, 0.f);
-        ov[k] = in ? __ldcg(reinterpret_cast<const float4*>(&scratch_o[(base + k) * 128 + d]))
-                   : make_float4(0.f, 0.f, 0.f, 0.f);
+        const int kk = min(k, n_splits - 1);
+        ml[k] = __ldcg(reinterpret_cast<const float2*>(&scratch_ml[(base + kk) * 2]));
+        ov[k] = __ldcg(reinterpret_cast<const float4*>(&scratch_o[(base + kk) * 128 + d]));
       }
       float mm = -INFINITY;
 #pragma unroll
-      for (int k = 0; k < 8; ++k) mm = fmaxf(mm, ml[k].x);
+      for (int k = 0; k < 8; ++k) mm = fmaxf(mm, ml[k].x);  // duplicates of the last chunk do not change a max
       const float mu = (mm == -INFINITY) ? 0.f : mm;
       float4 oo = make_float4(0.f, 0.f, 0.f, 0.f);
       float ll = 0.f;
@@ -394,6 +417,7 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
     }
   }
   if (tid == 0) counters[b * n_kv_heads + kvh] = 0;  // leave the counters zero for the next call
+  if (tid == 0) BCG_TL(4, 5);
 }
 
 template <int G>
@@ -548,3 +572,5 @@ int decode_attn_paged_static(const void* q, const void* kv_cache, const int* blo
 }
 
 }  // namespace bcg
+
+BCG_TL_DEFINE_DUMP(bcg_tl_dump_attn)

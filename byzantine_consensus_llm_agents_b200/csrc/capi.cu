@@ -44,6 +44,13 @@ int bcg_gemm_bf16_tn(const void* X, const void* W, void* out, int M, int N, int 
   return gemm_bf16_tn(X, W, out, M, N, K, ldx, ldw, ld_out, epilogue, splits, flags, S(stream));
 }
 
+int bcg_gemm_bf16_tn_fused(const void* X, const void* W, void* out, int M, int N, int K,
+                           long long ldx, long long ldw, long long ld_out, int epilogue, int splits,
+                           int flags, const bcg_gemm_fusion* fusion, void* stream) {
+  return gemm_bf16_tn_fused(X, W, out, M, N, K, ldx, ldw, ld_out, epilogue, splits, flags, fusion,
+                            S(stream));
+}
+
 int bcg_gemm_splits_for(int M, int N, int K) { return gemm_splits_for(M, N, K); }
 
 int bcg_embed_rmsnorm(const int* ids, const void* embed, const float* w, float* residual, void* xn,

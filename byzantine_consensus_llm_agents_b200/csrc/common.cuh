@@ -203,6 +203,42 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16_m128(int n) {
 }
 
 // ----------------------------------------------------------------------------
+// ----------------------------------------------------------------------------
+// Timeline instrumentation (dev tool, tools/timeline.py): compiled in only with -DBCG_TIMELINE,
+// into a separate library.  Chosen threads stamp %globaltimer into a per-translation-unit ring;
+// BCG_TL_DEFINE_DUMP(name) exports that unit's dump/reset function.
+// ----------------------------------------------------------------------------
+#ifdef BCG_TIMELINE
+constexpr unsigned kTlCap = 1u << 18;
+static __device__ unsigned long long g_tl[kTlCap];
+static __device__ unsigned int g_tl_n;
+__device__ __forceinline__ void tl_mark(unsigned id, unsigned phase) {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  const unsigned blk = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+  const unsigned i = atomicAdd(&g_tl_n, 1u);
+  if (i < kTlCap) g_tl[i] = (t << 20) | (static_cast<unsigned long long>(id) << 16) |
+                            (static_cast<unsigned long long>(phase) << 12) | (blk < 4095u ? blk : 4095u);
+}
+#define BCG_TL(id, phase) ::bcg::tl_mark(id, phase)
+#define BCG_TL_DEFINE_DUMP(name)                                                              \
+  extern "C" int name(unsigned long long* host, int cap, int reset) {                         \
+    unsigned n = 0;                                                                            \
+    if (cudaMemcpyFromSymbol(&n, ::bcg::g_tl_n, sizeof(n)) != cudaSuccess) return -1;          \
+    if (n > ::bcg::kTlCap) n = ::bcg::kTlCap;                                                  \
+    if (static_cast<int>(n) > cap) n = cap;                                                    \
+    if (n && cudaMemcpyFromSymbol(host, ::bcg::g_tl, n * sizeof(unsigned long long)) != cudaSuccess) return -1; \
+    if (reset) {                                                                               \
+      const unsigned z = 0;                                                                    \
+      if (cudaMemcpyToSymbol(::bcg::g_tl_n, &z, sizeof(z)) != cudaSuccess) return -1;          \
+    }                                                                                          \
+    return static_cast<int>(n);                                                                \
+  }
+#else
+#define BCG_TL(id, phase) ((void)0)
+#define BCG_TL_DEFINE_DUMP(name)
+#endif
+
 // programmatic dependent launch (PDL)
 // ----------------------------------------------------------------------------
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }

@@ -28,6 +28,7 @@ constexpr int kBlockK = 64;
 constexpr int kUmmaK = 16;
 constexpr int kGemmThreads = 192;
 
+constexpr int kSumsqStride = 128;  // rows per tile entry of the sum-of-squares tables (M <= 128)
 constexpr int kPreWaitStages = 6;  // weight slots requested before griddepcontrol.wait
 
 struct GemmArgs {
@@ -42,6 +43,21 @@ struct GemmArgs {
   long long ld_out;         // elements
   uint64_t hint_a, hint_b;
   int pdl_wait_b;           // 1: launched with programmatic stream serialization (see the producer)
+  // ---- decode-only fusions of the residual add + RMSNorm that sits between two projections
+  // consumer side: the activations are r*w (NOT yet divided by the row's RMS); every output row m is
+  // multiplied by rsqrt(sum_t scale_sumsq[t][m] / scale_d + scale_eps) in the epilogue
+  const float* scale_sumsq;  // [scale_tiles][kSumsqStride]
+  int scale_tiles;
+  int scale_d;
+  float scale_eps;
+  // producer side (split-K fp32 partials): the item that completes a 128-column tile adds the
+  // partials (index order) to the residual, writes it back, writes bf16(r*w) and the tile's
+  // per-row sum of squares
+  float* red_residual;       // [M][N] fp32, N == ld_out
+  const float* red_w;        // [N]
+  __nv_bfloat16* red_xn;     // [M][N]
+  float* red_sumsq;          // [tiles_a][kSumsqStride]
+  int* red_counters;         // [tiles_a], zero on entry, zero again on exit
 };
 
 __device__ __forceinline__ float silu_mul(float g, float u) {
@@ -67,10 +83,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   uint64_t* tmem_full = empty_bar + STAGES;
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  __shared__ float row_scale[kSumsqStride];
+  __shared__ int red_last;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   pdl_launch_dependents();
+  if (threadIdx.x == 0) BCG_TL(1, 0);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -138,6 +157,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         }
         pdl_wait();
       }
+      BCG_TL(1, 1);
       int stage = 0;
       uint32_t phase = 0;
       int idx = 0;
@@ -159,6 +179,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
           }
         }
       }
+      BCG_TL(1, 2);
     }
   } else if (warp == 1) {
     // ------------------------------ MMA issuer --------------------------------
@@ -201,6 +222,25 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     if (args.pdl_wait_b) pdl_wait();  // `out` may still be read by the previous kernel's consumers
     const int q = warp & 3;  // TMEM sub-partition this warp may read
     const int row = q * 32 + lane;
+    const int etid = threadIdx.x - 64;  // 0..127 over the four epilogue warps
+    if (args.scale_sumsq) {
+      // 1/RMS of every activation row from the per-tile sums the producing GEMM left behind,
+      // tiles added in index order (deterministic, the same for every CTA)
+      if (etid < args.M) {
+        float tot = 0.f;
+        for (int t0 = 0; t0 < args.scale_tiles; t0 += 8) {
+          float v[8];
+#pragma unroll
+          for (int t = 0; t < 8; ++t)
+            v[t] = (t0 + t < args.scale_tiles) ? __ldcg(args.scale_sumsq + (t0 + t) * kSumsqStride + etid) : 0.f;
+#pragma unroll
+          for (int t = 0; t < 8; ++t)
+            if (t0 + t < args.scale_tiles) tot += v[t];
+        }
+        row_scale[etid] = rsqrtf(tot / static_cast<float>(args.scale_d) + args.scale_eps);
+      }
+      asm volatile("bar.sync 2, 128;" ::: "memory");
+    }
     int acc = 0;
     uint32_t acc_phase = 0;
     const int M = args.M, N = args.N;
@@ -221,6 +261,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
           uint32_t v[16];
           tmem_ld_x16(taddr + c, v);
           tmem_ld_wait();
+          if (args.scale_sumsq) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              v[j] = __float_as_uint(__uint_as_float(v[j]) * row_scale[(m0 + c + j) & (kSumsqStride - 1)]);
+          }
           if (args.epi == BCG_EPI_F32) {
             float* o = reinterpret_cast<float*>(args.out) + static_cast<long long>(split) * M * ld;
 #pragma unroll
@@ -323,7 +368,68 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       mbar_arrive(&tmem_empty[acc]);
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
+      if (args.red_counters) {
+        // Which item completes this tile?  The four epilogue warps have stored their slab; one
+        // thread publishes that (barrier -> fence -> counter) and learns whether all `splits`
+        // slabs of the tile are now in L2.  Nobody waits for anybody: the last arrival reduces.
+        asm volatile("bar.sync 2, 128;" ::: "memory");
+        if (etid == 0) {
+          fence_acq_rel_gpu();
+          const int prev = atomicAdd(&args.red_counters[ta], 1);
+          fence_acq_rel_gpu();
+          red_last = (prev == args.splits - 1);
+          if (red_last) args.red_counters[ta] = 0;  // every arrival of this launch has happened
+        }
+        asm volatile("bar.sync 2, 128;" ::: "memory");
+        if (red_last) {
+          // warp e owns rows e, e+4, ...; a lane owns 4 consecutive columns of the tile.  Loads
+          // bypass L1 (other SMs wrote the data); two rows' worth are in flight at a time.
+          const int e = etid >> 5;
+          const int n = ta * kBlockA + lane * 4;
+          const float4 wv = *reinterpret_cast<const float4*>(args.red_w + n);
+          const float* P = reinterpret_cast<const float*>(args.out);
+          const long long slab = static_cast<long long>(M) * ld;
+          for (int mb = e; mb < M; mb += 8) {
+            float4 r[2], p[2][16];
+#pragma unroll
+            for (int u = 0; u < 2; ++u)
+              r[u] = __ldcg(reinterpret_cast<const float4*>(args.red_residual + min(mb + 4 * u, M - 1) * ld + n));
+            // unconditional (clamped) loads so that all of them are in flight before the first add
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+              const int m = min(mb + 4 * u, M - 1);
+#pragma unroll
+              for (int sp = 0; sp < 16; ++sp)
+                p[u][sp] = __ldcg(reinterpret_cast<const float4*>(P + min(sp, args.splits - 1) * slab + m * ld + n));
+            }
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+              const int m = mb + 4 * u;
+              if (m < M) {
+                float4 a = p[u][0];
+#pragma unroll
+                for (int sp = 1; sp < 16; ++sp) {
+                  if (sp < args.splits) {
+                    a.x += p[u][sp].x; a.y += p[u][sp].y; a.z += p[u][sp].z; a.w += p[u][sp].w;
+                  }
+                }
+                float4 x = r[u];
+                x.x += a.x; x.y += a.y; x.z += a.z; x.w += a.w;
+                *reinterpret_cast<float4*>(args.red_residual + m * ld + n) = x;
+                uint2 pk;
+                pk.x = pack_bf16(x.x * wv.x, x.y * wv.y);
+                pk.y = pack_bf16(x.z * wv.z, x.w * wv.w);
+                *reinterpret_cast<uint2*>(args.red_xn + m * ld + n) = pk;
+                float ss = __fmaf_rn(x.w, x.w, __fmaf_rn(x.z, x.z, __fmaf_rn(x.y, x.y, __fmul_rn(x.x, x.x))));
+                ss = warp_sum(ss);
+                if (lane == 0) args.red_sumsq[ta * kSumsqStride + m] = ss;
+              }
+            }
+          }
+        }
+      }
     }
+    if (threadIdx.x == 64) BCG_TL(1, 3);
   }
 
   tc_fence_before();
@@ -442,6 +548,12 @@ int gemm_splits_for(int M, int N, int K) {
 int gemm_bf16_tn(const void* X, const void* W, void* out, int M, int N, int K, long long ldx,
                  long long ldw, long long ld_out, int epi, int splits, int flags,
                  cudaStream_t stream) {
+  return gemm_bf16_tn_fused(X, W, out, M, N, K, ldx, ldw, ld_out, epi, splits, flags, nullptr, stream);
+}
+
+int gemm_bf16_tn_fused(const void* X, const void* W, void* out, int M, int N, int K, long long ldx,
+                       long long ldw, long long ld_out, int epi, int splits, int flags,
+                       const bcg_gemm_fusion* fu, cudaStream_t stream) {
   if (!X || !W || !out || M <= 0 || N <= 0 || K <= 0) {
     set_last_error("bcg_gemm_bf16_tn", "null pointer or non-positive dimension");
     return BCG_ERR_ARG;
@@ -477,6 +589,37 @@ int gemm_bf16_tn(const void* X, const void* W, void* out, int M, int N, int K, l
   a.out = out;
   a.ld_out = ld_out;
   a.pdl_wait_b = ((flags | launch_flags()) & BCG_GEMM_PDL) ? 1 : 0;
+  if (fu && (fu->scale_sumsq || fu->red_counters)) {
+    if (!swap || (fu->red_counters && (N % kBlockA))) {
+      set_last_error("bcg_gemm_bf16_tn_fused", "norm fusion needs M <= 128 (and N % 128 == 0 on the producer side)");
+      return BCG_ERR_ARG;
+    }
+    if (fu->scale_sumsq) {
+      if (fu->scale_tiles <= 0 || fu->scale_d <= 0) {
+        set_last_error("bcg_gemm_bf16_tn_fused", "scale_tiles and scale_d must be positive");
+        return BCG_ERR_ARG;
+      }
+      a.scale_sumsq = fu->scale_sumsq;
+      a.scale_tiles = fu->scale_tiles;
+      a.scale_d = fu->scale_d;
+      a.scale_eps = fu->scale_eps;
+    }
+    if (fu->red_counters) {
+      if (epi != BCG_EPI_F32 || splits > 16 || ld_out != N || !fu->red_residual || !fu->red_w ||
+          !fu->red_xn || !fu->red_sumsq || (reinterpret_cast<uintptr_t>(fu->red_residual) & 15) ||
+          (reinterpret_cast<uintptr_t>(fu->red_w) & 15) || (reinterpret_cast<uintptr_t>(fu->red_xn) & 7)) {
+        set_last_error("bcg_gemm_bf16_tn_fused",
+                       "producer fusion needs BCG_EPI_F32, splits <= 16, ld_out == N and aligned "
+                       "residual / weight / xn / sumsq buffers");
+        return BCG_ERR_ARG;
+      }
+      a.red_residual = fu->red_residual;
+      a.red_w = fu->red_w;
+      a.red_xn = reinterpret_cast<__nv_bfloat16*>(fu->red_xn);
+      a.red_sumsq = fu->red_sumsq;
+      a.red_counters = fu->red_counters;
+    }
+  }
   int bn;
   if (swap) {
     bn = M <= 16 ? 16 : M <= 32 ? 32 : M <= 64 ? 64 : 128;
@@ -515,3 +658,5 @@ int gemm_bf16_tn(const void* X, const void* W, void* out, int M, int N, int K, l
 }
 
 }  // namespace bcg
+
+BCG_TL_DEFINE_DUMP(bcg_tl_dump_gemm)

@@ -12,6 +12,9 @@ namespace bcg {
 int gemm_bf16_tn(const void* X, const void* W, void* out, int M, int N, int K, long long ldx,
                  long long ldw, long long ld_out, int epi, int splits, int flags,
                  cudaStream_t stream);
+int gemm_bf16_tn_fused(const void* X, const void* W, void* out, int M, int N, int K, long long ldx,
+                       long long ldw, long long ld_out, int epi, int splits, int flags,
+                       const bcg_gemm_fusion* fusion, cudaStream_t stream);
 int gemm_splits_for(int M, int N, int K);
 // TMA descriptor of a row-major bf16 matrix (rows x K, pitch ld elements): boxes of box_rows x 64
 // elements land in shared memory 128B-swizzled, out-of-bounds elements read as zero.

@@ -137,9 +137,39 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
     ~FlagScope() { launch_flags() = saved; }
   } scope(gf);
   float* P = ws->partials;
+  // Norm fusion (single GPU, opt-in with BCG_STEP_FUSED_NORM): the o / down projections finish the
+  // residual add and leave bf16(residual * w) plus per-tile sums of squares; the projection that
+  // follows applies 1/RMS in its epilogue.  No add_rmsnorm kernel runs after layer 0's embedding
+  // norm.  Measured SLOWER than the separate 8-CTA-cluster norm kernel (14B, 10 rows: 6.07 vs
+  // 5.93 ms per step): the fence + counter + reload chain at the end of the o / down GEMMs runs
+  // while HBM is saturated and costs 7-10 us, the stand-alone norm 4-5 us on an idle memory system.
+  const bool nf = tp == 1 && ws->row_sumsq && ws->tile_counters && (d % 128) == 0 && s_o <= 16 &&
+                  s_dn <= 16 && (flags & BCG_STEP_FUSED_NORM) && !skip_norm;
+  const int n_tiles_d = d / 128;
+  float* sumsq_attn = ws->row_sumsq;                      // written by o, read by gate_up
+  float* sumsq_mlp = ws->row_sumsq ? ws->row_sumsq + static_cast<long long>(n_tiles_d) * 128 : nullptr;  // down -> qkv / lm_head
+  auto consumer = [&](const float* table) {
+    bcg_gemm_fusion f = {};
+    f.scale_sumsq = table;
+    f.scale_tiles = n_tiles_d;
+    f.scale_d = d;
+    f.scale_eps = m->rms_eps;
+    return f;
+  };
+  auto producer = [&](float* table, const void* norm_w, void* xn_out) {
+    bcg_gemm_fusion f = {};
+    f.red_residual = ws->residual;
+    f.red_w = static_cast<const float*>(norm_w);
+    f.red_xn = xn_out;
+    f.red_sumsq = table;
+    f.red_counters = ws->tile_counters;
+    return f;
+  };
   for (int l = 0; l < m->n_layers; ++l) {
     if (l == 0) {
       BCG_TRY(embed_rmsnorm(ids, m->embed, m->ln1[0], ws->residual, ws->xn, B, d, m->rms_eps, st));
+    } else if (nf) {
+      // ws->xn and sumsq_mlp were produced by the previous layer's down projection
     } else if (fused) {
       BCG_TRY(tp_add_rmsnorm(ws->residual, off_dn, s_dn, static_cast<long long>(B) * d, m->ln1[l], ws->xn, 1,
                              B, d, m->rms_eps, st));
@@ -147,9 +177,11 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
       BCG_TRY(add_rmsnorm(ws->residual, P, 1, s_dn, static_cast<long long>(B) * d, m->ln1[l], ws->xn,
                           nullptr, B, d, m->rms_eps, st));
     }
-    if (!skip_qkv)
-    BCG_TRY(gemm_bf16_tn(ws->xn, m->w_qkv[l], P, B, qkv_dim, d, d, d, qkv_dim, BCG_EPI_F32, s_qkv, gf,
-                         st));
+    if (!skip_qkv) {
+      const bcg_gemm_fusion f = consumer(sumsq_mlp);
+      BCG_TRY(gemm_bf16_tn_fused(ws->xn, m->w_qkv[l], P, B, qkv_dim, d, d, d, qkv_dim, BCG_EPI_F32, s_qkv,
+                                 gf, (nf && l > 0) ? &f : nullptr, st));
+    }
     if (!skip_rope)
     BCG_TRY(qknorm_rope_kvwrite(P, 1, s_qkv, static_cast<long long>(B) * qkv_dim, qkv_dim,
                                 m->q_norm ? m->q_norm[l] : nullptr,
@@ -167,6 +199,11 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
       BCG_TRY(tp_signal(0, st));
       BCG_TRY(tp_add_rmsnorm(ws->residual, off_o, s_o, static_cast<long long>(B) * d, m->ln2[l], ws->xn, 0, B,
                              d, m->rms_eps, st));
+    } else if (nf) {
+      const bcg_gemm_fusion f = producer(sumsq_attn, m->ln2[l], ws->xn);
+      if (!skip_o)
+      BCG_TRY(gemm_bf16_tn_fused(ws->attn, m->w_o[l], P, B, d, hq * 128, hq * 128, hq * 128, d, BCG_EPI_F32,
+                                 s_o, gf, &f, st));
     } else {
     if (!skip_o)
     BCG_TRY(gemm_bf16_tn(ws->attn, m->w_o[l], P, B, d, hq * 128, hq * 128, hq * 128, d, BCG_EPI_F32,
@@ -178,25 +215,34 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
     BCG_TRY(add_rmsnorm(ws->residual, P, 1, s_o, static_cast<long long>(B) * d, m->ln2[l], ws->xn,
                         nullptr, B, d, m->rms_eps, st));
     }
+    const bcg_gemm_fusion f_gu = consumer(sumsq_attn);
     if (skip_gu) {
     } else if (s_gu == 1) {
-      BCG_TRY(gemm_bf16_tn(ws->xn, m->w_gate_up[l], ws->act, B, 2 * ff, d, d, d, ff, BCG_EPI_SWIGLU, 1,
-                           gf, st));
+      BCG_TRY(gemm_bf16_tn_fused(ws->xn, m->w_gate_up[l], ws->act, B, 2 * ff, d, d, d, ff, BCG_EPI_SWIGLU, 1,
+                                 gf, nf ? &f_gu : nullptr, st));
     } else {
-      BCG_TRY(gemm_bf16_tn(ws->xn, m->w_gate_up[l], P, B, 2 * ff, d, d, d, 2 * ff, BCG_EPI_F32, s_gu,
-                           gf, st));
+      BCG_TRY(gemm_bf16_tn_fused(ws->xn, m->w_gate_up[l], P, B, 2 * ff, d, d, d, 2 * ff, BCG_EPI_F32, s_gu,
+                                 gf, nf ? &f_gu : nullptr, st));
       BCG_TRY(swiglu_reduce(P, s_gu, static_cast<long long>(B) * 2 * ff, ws->act, B, 2 * ff, st));
     }
     if (fused) {
       BCG_TRY(gemm_bf16_tn(ws->act, m->w_down[l], sym + off_dn, B, d, ff, ff, ff, d, BCG_EPI_F32, s_dn, gf, st));
       BCG_TRY(tp_signal(1, st));
+    } else if (nf) {
+      const bool last = (l + 1 == m->n_layers);
+      const bcg_gemm_fusion f = producer(sumsq_mlp, last ? m->final_norm : m->ln1[l + 1],
+                                         last ? ws->xn_last : ws->xn);
+      if (!skip_dn)
+      BCG_TRY(gemm_bf16_tn_fused(ws->act, m->w_down[l], P, B, d, ff, ff, ff, d, BCG_EPI_F32, s_dn, gf, &f, st));
     } else {
       if (!skip_dn)
       BCG_TRY(gemm_bf16_tn(ws->act, m->w_down[l], P, B, d, ff, ff, ff, d, BCG_EPI_F32, s_dn, gf, st));
       if (tp > 1) BCG_TRY(tp_all_reduce_f32(P, static_cast<long long>(s_dn) * B * d, st));
     }
   }
-  if (fused) {
+  if (nf) {
+    // ws->xn_last and sumsq_mlp come from the last layer's down projection
+  } else if (fused) {
     BCG_TRY(tp_add_rmsnorm(ws->residual, off_dn, s_dn, static_cast<long long>(B) * d, m->final_norm,
                            ws->xn_last, 1, B, d, m->rms_eps, st));
   } else {
@@ -208,8 +254,9 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
                          BCG_EPI_F32, 1, gf, st));
     BCG_TRY(tp_all_gather_f32(ws->logits_local, ws->logits, static_cast<long long>(B) * m->vocab, st));
   } else if (!skip_lm) {
-    BCG_TRY(gemm_bf16_tn(ws->xn_last, m->lm_head, ws->logits, B, m->vocab, d, d, d, m->vocab,
-                         BCG_EPI_F32, 1, gf, st));
+    const bcg_gemm_fusion f = consumer(sumsq_mlp);
+    BCG_TRY(gemm_bf16_tn_fused(ws->xn_last, m->lm_head, ws->logits, B, m->vocab, d, d, d, m->vocab,
+                               BCG_EPI_F32, 1, gf, nf ? &f : nullptr, st));
   }
   return BCG_OK;
 }

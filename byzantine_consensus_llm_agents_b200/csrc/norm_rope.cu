@@ -125,9 +125,12 @@ __device__ __forceinline__ float4 residual_plus_delta(const float* __restrict__ 
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
   for (int s0 = 0; s0 < n_partials; s0 += BATCH) {
     float4 p[BATCH];
+    // Unconditional loads (slabs past the end re-read the last one and are ignored below): with
+    // a predicate per load the compiler runs out of predicate registers and interleaves loads
+    // with the dependent adds, which turns one memory round trip into three.
 #pragma unroll
     for (int s = 0; s < BATCH; ++s)
-      if (s0 + s < n_partials) p[s] = *reinterpret_cast<const float4*>(dp + (s0 + s) * partial_stride);
+      p[s] = *reinterpret_cast<const float4*>(dp + min(s0 + s, n_partials - 1) * partial_stride);
 #pragma unroll
     for (int s = 0; s < BATCH; ++s) {
       if (s0 + s < n_partials) {
@@ -161,7 +164,9 @@ add_rmsnorm_cluster_kernel(float* __restrict__ residual, const void* __restrict_
   __shared__ float seg_ss;                 // this segment's sum of squares (read by the peers)
   __shared__ float all_ss[kNormSegments];
   pdl_launch_dependents();
+  if (threadIdx.x == 0) BCG_TL(2, 0);
   pdl_wait();
+  if (threadIdx.x == 0) BCG_TL(2, 1);
   const int seg = blockIdx.x;  // == rank in the cluster
   const int t = blockIdx.y;
   const long long src = src_rows ? src_rows[t] : t;
@@ -204,6 +209,7 @@ add_rmsnorm_cluster_kernel(float* __restrict__ residual, const void* __restrict_
       norm_store(residual, xn, !src_rows, static_cast<long long>(t) * d + v * 4, x[i], ww[i], inv);
   }
   cluster.barrier_wait();  // nobody leaves while a peer may still read its seg_ss
+  if (threadIdx.x == 0) BCG_TL(2, 3);
 }
 
 // One CTA per row; physical warp pw plays virtual warps pw and pw + 32 (see the order above).
@@ -281,7 +287,9 @@ qknorm_rope_kvwrite_kernel(const void* __restrict__ qkv, int qkv_is_f32, int n_p
                            __nv_bfloat16* __restrict__ kv_cache, int T, int n_heads, int n_kv_heads,
                            int page_size, float eps) {
   pdl_launch_dependents();
+  if (threadIdx.x == 0) BCG_TL(3, 0);
   pdl_wait();
+  if (threadIdx.x == 0) BCG_TL(3, 1);
   const int lane = threadIdx.x & 31;
   const int heads_total = n_heads + 2 * n_kv_heads;
   const long long wid = static_cast<long long>(blockIdx.x) * 4 + (threadIdx.x >> 5);
@@ -437,3 +445,5 @@ int swiglu_reduce(const float* partials, int n_partials, long long partial_strid
 }
 
 }  // namespace bcg
+
+BCG_TL_DEFINE_DUMP(bcg_tl_dump_norm)

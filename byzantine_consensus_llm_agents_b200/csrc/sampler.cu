@@ -87,7 +87,8 @@ mask_sample_kernel(const SamplerDev p) {
   cg::cluster_group cluster = cg::this_cluster();
   __shared__ Best warp_best[kSampThreads / 32];
   __shared__ Best cta_best[kSampCluster];  // only CTA 0's copy is used
-  pdl_launch_dependents();
+  // No early griddepcontrol.launch_dependents here: this kernel writes seq_lens / slot_map, which
+  // the next step's decode attention reads before its own dependency wait (attn_decode.cu).
   pdl_wait();
 
   const int row = blockIdx.y;
@@ -201,7 +202,8 @@ mask_sample_kernel(const SamplerDev p) {
 
 // n_active[0] = number of rows still running (one small block; lets the host poll one int).
 __global__ void count_active_kernel(const int* __restrict__ finished, int B, int* n_active) {
-  pdl_launch_dependents();
+  // No early griddepcontrol.launch_dependents here: this kernel writes seq_lens / slot_map, which
+  // the next step's decode attention reads before its own dependency wait (attn_decode.cu).
   pdl_wait();
   int c = 0;
   for (int i = threadIdx.x; i < B; i += 32) c += (finished[i] == 0);

@@ -146,6 +146,7 @@ class Engine:
                  max_rows: int = 64, prefill_tokens: int = 16384, kv_pages: Optional[int] = None,
                  gpu_memory_utilization: float = 0.9, base_seed: int = 0, device: str = "cuda:0",
                  enable_prefix_cache: bool = True, use_cuda_graph: bool = True, pdl: bool = False,
+                 fused_norm: bool = False,
                  tp_rank: int = 0, tp_size: int = 1, tp_fused_allreduce: bool = True, tp_group=None):
         """`cfg` is the FULL architecture; with tp_size > 1 `weights` must be this rank's shard
         (Weights.shard / random_init_sharded) and bcg_tp_init must have been called (collective)."""
@@ -168,7 +169,7 @@ class Engine:
         self.calls = 0
         self.enable_prefix_cache = enable_prefix_cache
         self.use_cuda_graph = use_cuda_graph
-        self.flags = L.GEMM_PDL if pdl else 0
+        self.flags = (L.GEMM_PDL if pdl else 0) | (L.STEP_FUSED_NORM if fused_norm else 0)
         self.max_blocks = (self.max_model_len + PAGE - 1) // PAGE
         self.max_steps = self.max_model_len
 
@@ -188,6 +189,7 @@ class Engine:
             so=z(B * lc.n_heads * self.max_splits_cap * 128, dt=f32),
             sml=z(B * lc.n_heads * self.max_splits_cap * 2, dt=f32),
             attn_counters=z(B * lc.n_kv_heads, dt=i32),
+            row_sumsq=z(2 * ((d + 127) // 128) * 128, dt=f32), tile_counters=z((d + 127) // 128, dt=i32),
             logits=z(B, full_cfg.vocab, dt=f32), xn_last=z(B, d))
         if tp_size > 1:
             self.buf["logits_local"] = z(B, lc.vocab, dt=f32)
@@ -202,6 +204,10 @@ class Engine:
         ws.max_splits = self.max_splits_cap
         ws.logits, ws.xn_last, ws.T_max, ws.B_max = b["logits"].data_ptr(), b["xn_last"].data_ptr(), T, B
         ws.logits_local = b["logits_local"].data_ptr() if tp_size > 1 else None
+        # tables for the opt-in norm fusion (fused_norm=True; single-GPU engines, d_model % 128 == 0)
+        fuse_norm = tp_size == 1 and d % 128 == 0
+        ws.row_sumsq = b["row_sumsq"].data_ptr() if fuse_norm else None
+        ws.tile_counters = b["tile_counters"].data_ptr() if fuse_norm else None
         ws.tp_region_floats = 0
         if tp_size > 1 and tp_fused_allreduce:
             # decode all-reduces fused into the norm kernels over NVLink peer memory

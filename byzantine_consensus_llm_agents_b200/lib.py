@@ -14,6 +14,7 @@ LIB_PATH = PKG / "_lib" / "libbcg_b200.so"
 
 EPI_BF16, EPI_F32, EPI_SWIGLU = 0, 1, 2
 GEMM_PDL = 1
+STEP_FUSED_NORM = 0x20000   # bcg_model_decode: fold add+RMSNorm into the GEMMs (opt-in, slower)
 
 c_int_p = C.POINTER(C.c_int)
 c_float_p = C.POINTER(C.c_float)
@@ -40,6 +41,13 @@ class SamplerArgs(C.Structure):
     ]
 
 
+class GemmFusion(C.Structure):
+    _fields_ = [
+        ("scale_sumsq", vp), ("scale_tiles", C.c_int), ("scale_d", C.c_int), ("scale_eps", C.c_float),
+        ("red_residual", vp), ("red_w", vp), ("red_xn", vp), ("red_sumsq", vp), ("red_counters", vp),
+    ]
+
+
 class Model(C.Structure):
     _fields_ = [
         ("n_layers", C.c_int), ("d_model", C.c_int), ("n_heads", C.c_int), ("n_kv_heads", C.c_int),
@@ -62,6 +70,7 @@ class Workspace(C.Structure):
         ("max_splits", C.c_int),
         ("logits", vp), ("logits_local", vp), ("tp_region_floats", C.c_longlong), ("xn_last", vp),
         ("T_max", C.c_int), ("B_max", C.c_int),
+        ("row_sumsq", vp), ("tile_counters", vp),
     ]
 
 
@@ -70,6 +79,9 @@ _SIGS = {
     "bcg_last_error": (C.c_char_p, []),
     "bcg_gemm_bf16_tn": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_longlong,
                                    C.c_longlong, C.c_longlong, C.c_int, C.c_int, C.c_int, vp]),
+    "bcg_gemm_bf16_tn_fused": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_longlong,
+                                         C.c_longlong, C.c_longlong, C.c_int, C.c_int, C.c_int,
+                                         C.POINTER(GemmFusion), vp]),
     "bcg_gemm_splits_for": (C.c_int, [C.c_int, C.c_int, C.c_int]),
     "bcg_embed_rmsnorm": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, vp]),
     "bcg_add_rmsnorm": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_longlong, vp, vp, vp, C.c_int,

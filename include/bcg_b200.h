@@ -52,6 +52,32 @@ const char* bcg_last_error(void);
 int bcg_gemm_bf16_tn(const void* X, const void* W, void* out, int M, int N, int K, long long ldx,
                      long long ldw, long long ld_out, int epilogue, int splits, int flags,
                      void* stream);
+/* Decode-only fusion of the `fused_add_rms_norm` that vLLM runs between two projections
+ * (vLLM model_executor/layers/layernorm.py RMSNorm.forward_cuda with a residual;
+ * models/qwen3.py:216-236 decoder layer) into the projections on either side of it, so that the
+ * norm costs no kernel of its own.  M <= 128, N % 128 == 0, ld_out == N for the producer side.
+ *   producer (red_counters != NULL; BCG_EPI_F32, splits <= 16): the work item that completes a
+ *     128-column tile adds the split-K partials (index order) to red_residual, writes it back,
+ *     writes red_xn = bf16(residual * red_w) — NOT yet divided by the row's RMS — and the tile's
+ *     per-row sum of squares to red_sumsq[tile][128].  red_counters: N/128 ints, zero on entry,
+ *     zero again on exit.
+ *   consumer (scale_sumsq != NULL): X is such a red_xn; every output row m is multiplied by
+ *     rsqrt(sum_t scale_sumsq[t][m] / scale_d + scale_eps) in the epilogue (tiles added in order).
+ * Either half may be unused (NULL). */
+typedef struct bcg_gemm_fusion {
+  const float* scale_sumsq;
+  int scale_tiles;
+  int scale_d;
+  float scale_eps;
+  float* red_residual;
+  const float* red_w;
+  void* red_xn;
+  float* red_sumsq;
+  int* red_counters;
+} bcg_gemm_fusion;
+int bcg_gemm_bf16_tn_fused(const void* X, const void* W, void* out, int M, int N, int K,
+                           long long ldx, long long ldw, long long ld_out, int epilogue, int splits,
+                           int flags, const bcg_gemm_fusion* fusion, void* stream);
 /* Split-K factor the engine uses for a decode GEMM of this shape (host helper, no GPU work). */
 int bcg_gemm_splits_for(int M, int N, int K);
 
@@ -238,6 +264,9 @@ typedef struct bcg_workspace {
                                  symmetric buffer, >= max(splits_o, splits_down) * B_max * d_model */
   void* xn_last;      /* bf16 [B_max, d_model] */
   int T_max, B_max;
+  /* decode norm fusion (bcg_gemm_bf16_tn_fused); both NULL = separate add_rmsnorm kernels */
+  float* row_sumsq;   /* fp32 [2][d_model/128][128]: per-tile row sums of squares, one table per norm */
+  int* tile_counters; /* int32 [d_model/128], zero-initialised once */
 } bcg_workspace;
 
 /* T new tokens (ragged over sequences) -> KV cache filled, logits of each sequence's last
@@ -249,7 +278,11 @@ int bcg_model_prefill(const bcg_model* m, const bcg_workspace* ws, const int* id
                       const int* last_rows, int n_seqs, int T, void* stream);
 /* One decode step for B rows: ids/positions/slot_map/seq_lens are the arrays bcg_mask_sample
  * maintains; logits land in ws->logits[0..B).  Stands in for one decode step of the same vLLM
- * forward. */
+ * forward.  flags: BCG_GEMM_PDL; BCG_STEP_FUSED_NORM folds the residual add +
+ * RMSNorm into the projections around it (bcg_gemm_bf16_tn_fused; needs ws->row_sumsq and
+ * ws->tile_counters, single GPU).  Off by default: measured slower than the separate cluster
+ * kernel. */
+#define BCG_STEP_FUSED_NORM 0x20000
 int bcg_model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids,
                      const int* positions, const int* slot_map, const int* seq_lens,
                      const int* block_table, int max_blocks_per_seq, int B, int flags,

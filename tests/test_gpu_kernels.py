@@ -146,6 +146,115 @@ def _rmsnorm_ref(x, w, eps):
     return x * torch.rsqrt(v + eps) * w
 
 
+# ------------------------------------------------------------------ GEMM with the norm folded in
+
+def _fusion(**kw):
+    f = L.GemmFusion()
+    for k, v in kw.items():
+        setattr(f, k, v.data_ptr() if torch.is_tensor(v) else v)
+    return f
+
+
+@pytest.mark.parametrize("M,N,K,splits", [(10, 5120, 5120, 7), (10, 5120, 17408, 11), (1, 256, 512, 2),
+                                          (16, 1024, 1024, 1), (33, 384, 2048, 16), (128, 256, 256, 3)])
+def test_gemm_producer_finishes_residual_and_norm_statistics(M, N, K, splits):
+    """bcg_gemm_bf16_tn_fused, producer half: split-K slabs -> residual (same fp32 order as
+    bcg_add_rmsnorm), bf16(residual*w), per-tile row sums of squares; counters back at zero."""
+    import ctypes as C
+    lib = _lib()
+    x = _rand_bf16(M, K, seed=31)
+    w = _rand_bf16(N, K, scale=0.05, seed=32)
+    res0 = torch.randn(M, N, device=DEV)
+    res = res0.clone()
+    nw = (torch.rand(N, device=DEV) + 0.5).float()
+    P = torch.full((splits, M, N), float("nan"), device=DEV)
+    xn = torch.zeros(M, N, device=DEV, dtype=torch.bfloat16)
+    tiles = N // 128
+    sumsq = torch.full((tiles, 128), float("nan"), device=DEV)
+    counters = torch.zeros(tiles, device=DEV, dtype=torch.int32)
+    f = _fusion(red_residual=res, red_w=nw, red_xn=xn, red_sumsq=sumsq, red_counters=counters)
+    for _ in range(2):  # twice: the counters must come back to zero
+        res.copy_(res0)
+        L.check(lib.bcg_gemm_bf16_tn_fused(x.data_ptr(), w.data_ptr(), P.data_ptr(), M, N, K, K, K, N, L.EPI_F32,
+                                           splits, 0, C.byref(f), L.stream_ptr()))
+        torch.cuda.synchronize()
+        assert int(counters.abs().sum()) == 0
+        acc = P[0].clone()
+        for sp in range(1, splits):
+            acc = acc + P[sp]
+        want = res0 + acc
+        assert torch.equal(res, want)                                   # same operation order
+        assert torch.equal(xn, (want * nw).to(torch.bfloat16))          # r*w rounded once
+        ss = want.view(M, tiles, 128).pow(2).sum(-1).T                  # [tiles, M]
+        assert torch.allclose(sumsq[:, :M], ss, rtol=1e-5, atol=1e-6)
+    # the partial slabs are an ordinary split-K result
+    ref = x.float() @ w.float().T
+    assert ((acc - ref).abs() <= ref.abs() * 2 ** -9 + 2e-3).all()
+
+
+@pytest.mark.parametrize("epi", ["f32", "bf16", "swiglu"])
+def test_gemm_consumer_applies_row_scale(epi):
+    import ctypes as C
+    lib = _lib()
+    M, N, K, d = 10, 1024, 2048, 2048
+    tiles = d // 128
+    x = _rand_bf16(M, K, seed=41)
+    w = _rand_bf16(N, K, scale=0.05, seed=42)
+    sumsq = torch.rand(tiles, 128, device=DEV) * 300 + 1.0
+    scale = torch.rsqrt(sumsq[:, :M].sum(0) / d + 1e-6)                  # [M]
+    f = _fusion(scale_sumsq=sumsq, scale_tiles=tiles, scale_d=d, scale_eps=1e-6)
+    if epi == "f32":
+        splits = 3
+        plain = torch.zeros(splits, M, N, device=DEV)
+        fused = torch.zeros(splits, M, N, device=DEV)
+        L.gemm(x, w, plain, L.EPI_F32, splits=splits)
+        L.check(lib.bcg_gemm_bf16_tn_fused(x.data_ptr(), w.data_ptr(), fused.data_ptr(), M, N, K, K, K, N,
+                                           L.EPI_F32, splits, 0, C.byref(f), L.stream_ptr()))
+        torch.cuda.synchronize()
+        # one fp32 multiply per element; the tile sums are added in index order
+        tot = torch.zeros(M, device=DEV)
+        for t in range(tiles):
+            tot = tot + sumsq[t, :M]
+        exact = torch.rsqrt(tot / d + 1e-6)
+        assert torch.allclose(fused, plain * exact[None, :, None], rtol=3e-7, atol=0)
+    else:
+        ref = (x.float() @ w.float().T) * scale[:, None]
+        if epi == "bf16":
+            out = torch.zeros(M, N, device=DEV, dtype=torch.bfloat16)
+            L.check(lib.bcg_gemm_bf16_tn_fused(x.data_ptr(), w.data_ptr(), out.data_ptr(), M, N, K, K, K, N,
+                                               L.EPI_BF16, 1, 0, C.byref(f), L.stream_ptr()))
+        else:
+            out = torch.zeros(M, N // 2, device=DEV, dtype=torch.bfloat16)
+            L.check(lib.bcg_gemm_bf16_tn_fused(x.data_ptr(), w.data_ptr(), out.data_ptr(), M, N, K, K, K, N // 2,
+                                               L.EPI_SWIGLU, 1, 0, C.byref(f), L.stream_ptr()))
+            r = ref.view(M, N // 32, 2, 16)
+            ref = (torch.nn.functional.silu(r[:, :, 0]) * r[:, :, 1]).reshape(M, N // 2)
+        torch.cuda.synchronize()
+        assert ((out.float() - ref).abs() <= ref.abs() * 2 ** -6 + 2e-3).all()
+
+
+def test_gemm_fusion_argument_checks():
+    import ctypes as C
+    lib = _lib()
+    M, N, K = 4, 256, 256
+    x, w = _rand_bf16(M, K), _rand_bf16(N, K)
+    P = torch.zeros(2, M, N, device=DEV)
+    res = torch.zeros(M, N, device=DEV)
+    nw = torch.ones(N, device=DEV)
+    xn = torch.zeros(M, N, device=DEV, dtype=torch.bfloat16)
+    sumsq = torch.zeros(2, 128, device=DEV)
+    cnt = torch.zeros(2, device=DEV, dtype=torch.int32)
+    f = _fusion(red_residual=res, red_w=nw, red_xn=xn, red_sumsq=sumsq, red_counters=cnt)
+    call = lambda m, n, epi, ld: lib.bcg_gemm_bf16_tn_fused(x.data_ptr(), w.data_ptr(), P.data_ptr(), m, n, K, K, K,
+                                                            ld, epi, 1, 0, C.byref(f), L.stream_ptr())
+    assert call(M, N, L.EPI_BF16, N) != 0           # producer needs the fp32 partial epilogue
+    assert call(M, 192, L.EPI_F32, 192) != 0        # N % 128
+    assert call(M, N, L.EPI_F32, N + 8) != 0        # ld_out == N
+    assert b"fusion" in lib.bcg_last_error()
+    assert call(M, N, L.EPI_F32, N) == 0
+    torch.cuda.synchronize()
+
+
 @pytest.mark.parametrize("T,d", [(1, 256), (10, 1024), (37, 5120), (5, 8192)])
 def test_embed_rmsnorm(T, d):
     lib = _lib()

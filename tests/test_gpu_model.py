@@ -73,6 +73,26 @@ def test_logits_match_fp32_cpu_forward(cfg, tol):
     print(f"{cfg.name}: worst |dlogit| = {worst:.4f}")
 
 
+@pytest.mark.parametrize("cfg", [TINY_QWEN, TINY_MISTRAL], ids=lambda c: c.name)
+def test_fused_norm_decode_path_matches_fp32_forward(cfg):
+    """Opt-in decode variant with the residual add + RMSNorm folded into the GEMMs
+    (bcg_gemm_bf16_tn_fused): same tolerance against the fp32 CPU forward, and the same greedy
+    tokens as the default path wherever the fp32 margin is clear."""
+    hf, eng, tk = _setup(cfg, fused_norm=True, pdl=True)
+    rng = np.random.default_rng(0)
+    lens = [5, 64, 200]
+    n_new = 10
+    prompts = _prompts(tk, rng, lens)
+    forced = [rng.integers(*tk.regular_range, size=n_new).tolist() for _ in lens]
+    eng.debug_logits = []
+    eng.generate([Request("", None, 0.0, n_new, forced=f, prompt_ids=p) for p, f in zip(prompts, forced)])
+    got = torch.stack(eng.debug_logits).cpu()
+    for b, (p, f) in enumerate(zip(prompts, forced)):
+        ref = full_logits(hf, p + f[:-1])[len(p) - 1:]
+        assert (got[:, b] - ref).abs().max().item() <= LOGIT_TOL
+    assert int(eng.buf["tile_counters"].abs().sum()) == 0
+
+
 def test_prefix_cache_reuse_is_exact():
     hf, eng, tk = _setup(TINY_QWEN)
     rng = np.random.default_rng(1)

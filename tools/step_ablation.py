@@ -30,6 +30,8 @@ def main():
     ap.add_argument("--rows", type=int, default=10)
     ap.add_argument("--ctx", type=int, default=1600)
     ap.add_argument("--pdl", type=int, default=1)
+    ap.add_argument("--base-flags", type=lambda x: int(x, 0), default=0,
+                    help="extra bcg_model_decode flags for every run, e.g. 0x20000 = norm folded into the GEMMs")
     a = ap.parse_args()
     cfg = PRESETS[a.model]
     dev = torch.device("cuda:0")
@@ -53,7 +55,7 @@ def main():
         L.check(eng.lib.bcg_model_decode(C.byref(eng.model.struct), C.byref(eng.ws), r["next_ids"].data_ptr(),
                                          r["positions"].data_ptr(), r["slot_map"].data_ptr(),
                                          r["seq_lens"].data_ptr(), r["block_table"].data_ptr(), eng.max_blocks, B,
-                                         eng.flags | extra, L.stream_ptr()))
+                                         eng.flags | extra | a.base_flags, L.stream_ptr()))
 
     def time_step(extra, reps=30):
         reset()
