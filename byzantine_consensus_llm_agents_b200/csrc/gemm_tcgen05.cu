@@ -383,48 +383,35 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         asm volatile("bar.sync 2, 128;" ::: "memory");
         if (red_last) {
           // warp e owns rows e, e+4, ...; a lane owns 4 consecutive columns of the tile.  Loads
-          // bypass L1 (other SMs wrote the data); two rows' worth are in flight at a time.
+          // bypass L1 (other SMs wrote the data); one row's worth is in flight at a time.
           const int e = etid >> 5;
           const int n = ta * kBlockA + lane * 4;
           const float4 wv = *reinterpret_cast<const float4*>(args.red_w + n);
           const float* P = reinterpret_cast<const float*>(args.out);
           const long long slab = static_cast<long long>(M) * ld;
-          for (int mb = e; mb < M; mb += 8) {
-            float4 r[2], p[2][16];
-#pragma unroll
-            for (int u = 0; u < 2; ++u)
-              r[u] = __ldcg(reinterpret_cast<const float4*>(args.red_residual + min(mb + 4 * u, M - 1) * ld + n));
+          for (int m = e; m < M; m += 4) {
+            float4 p[16];
             // unconditional (clamped) loads so that all of them are in flight before the first add
+            float4 x = __ldcg(reinterpret_cast<const float4*>(args.red_residual + m * ld + n));
 #pragma unroll
-            for (int u = 0; u < 2; ++u) {
-              const int m = min(mb + 4 * u, M - 1);
+            for (int sp = 0; sp < 16; ++sp)
+              p[sp] = __ldcg(reinterpret_cast<const float4*>(P + min(sp, args.splits - 1) * slab + m * ld + n));
+            float4 a = p[0];
 #pragma unroll
-              for (int sp = 0; sp < 16; ++sp)
-                p[u][sp] = __ldcg(reinterpret_cast<const float4*>(P + min(sp, args.splits - 1) * slab + m * ld + n));
-            }
-#pragma unroll
-            for (int u = 0; u < 2; ++u) {
-              const int m = mb + 4 * u;
-              if (m < M) {
-                float4 a = p[u][0];
-#pragma unroll
-                for (int sp = 1; sp < 16; ++sp) {
-                  if (sp < args.splits) {
-                    a.x += p[u][sp].x; a.y += p[u][sp].y; a.z += p[u][sp].z; a.w += p[u][sp].w;
-                  }
-                }
-                float4 x = r[u];
-                x.x += a.x; x.y += a.y; x.z += a.z; x.w += a.w;
-                *reinterpret_cast<float4*>(args.red_residual + m * ld + n) = x;
-                uint2 pk;
-                pk.x = pack_bf16(x.x * wv.x, x.y * wv.y);
-                pk.y = pack_bf16(x.z * wv.z, x.w * wv.w);
-                *reinterpret_cast<uint2*>(args.red_xn + m * ld + n) = pk;
-                float ss = __fmaf_rn(x.w, x.w, __fmaf_rn(x.z, x.z, __fmaf_rn(x.y, x.y, __fmul_rn(x.x, x.x))));
-                ss = warp_sum(ss);
-                if (lane == 0) args.red_sumsq[ta * kSumsqStride + m] = ss;
+            for (int sp = 1; sp < 16; ++sp) {
+              if (sp < args.splits) {
+                a.x += p[sp].x; a.y += p[sp].y; a.z += p[sp].z; a.w += p[sp].w;
               }
             }
+            x.x += a.x; x.y += a.y; x.z += a.z; x.w += a.w;
+            *reinterpret_cast<float4*>(args.red_residual + m * ld + n) = x;
+            uint2 pk;
+            pk.x = pack_bf16(x.x * wv.x, x.y * wv.y);
+            pk.y = pack_bf16(x.z * wv.z, x.w * wv.w);
+            *reinterpret_cast<uint2*>(args.red_xn + m * ld + n) = pk;
+            float ss = __fmaf_rn(x.w, x.w, __fmaf_rn(x.z, x.z, __fmaf_rn(x.y, x.y, __fmul_rn(x.x, x.x))));
+            ss = warp_sum(ss);
+            if (lane == 0) args.red_sumsq[ta * kSumsqStride + m] = ss;
           }
         }
       }
