@@ -1,7 +1,9 @@
 // extern "C" surface declared in include/bcg_b200.h.
 #include <string.h>
 
+#include <mutex>
 #include <string>
+#include <unordered_set>
 
 #include "common.cuh"
 #include "kernels.h"
@@ -13,6 +15,16 @@ static thread_local std::string g_last_error;
 int& launch_flags() {
   static thread_local int flags = 0;
   return flags;
+}
+
+void prefer_max_smem_carveout(const void* kernel) {
+  static std::mutex mu;
+  static std::unordered_set<const void*> done;
+  std::lock_guard<std::mutex> lock(mu);
+  if (done.insert(kernel).second &&
+      cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                           cudaSharedmemCarveoutMaxShared) != cudaSuccess)
+    (void)cudaGetLastError();  // a hint; failing to set it is harmless
 }
 
 void set_last_error(const char* what, const char* detail) {

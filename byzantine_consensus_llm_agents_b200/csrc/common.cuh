@@ -37,9 +37,17 @@ void set_last_error(const char* what, const char* detail);
 // predecessor's results with griddepcontrol.wait before touching them.
 int& launch_flags();
 
+// An SM runs CTAs of different kernels side by side only if they agree on its L1 / shared-memory
+// split.  The GEMM and attention CTAs need the largest shared-memory carve-out; a small kernel left
+// at its default (mostly-L1) split cannot become resident next to them, so under programmatic
+// dependent launch it would start only after they exit — and so would ITS dependents.  Every
+// kernel launched through launch_k therefore asks for the same maximum carve-out (once).
+void prefer_max_smem_carveout(const void* kernel);
+
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
                             cudaStream_t stream, Args&&... args) {
+  prefer_max_smem_carveout(reinterpret_cast<const void*>(kernel));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = block;

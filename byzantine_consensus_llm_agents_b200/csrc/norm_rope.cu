@@ -100,7 +100,7 @@ embed_rmsnorm_kernel(const int* __restrict__ ids, const __nv_bfloat16* __restric
 constexpr int kNormSegments = 8;
 constexpr int kSegThreads = 256;
 constexpr int kSegTurns = 2;  // d <= 8 * 256 * 2 * 4 = 16384
-constexpr int kPartialsInFlight = 16;
+constexpr int kPartialsInFlight = 12;
 constexpr int kNormClusterMaxRows = 128;  // decode-sized launches take the cluster kernel
 
 __device__ __forceinline__ float sumsq4(const float4& x) {
@@ -153,7 +153,13 @@ __device__ __forceinline__ void norm_store(float* __restrict__ residual, __nv_bf
   store_bf16x4(xn + off, x.x * inv * ww.x, x.y * inv * ww.y, x.z * inv * ww.z, x.w * inv * ww.w);
 }
 
-__global__ void __cluster_dims__(kNormSegments, 1, 1) __launch_bounds__(kSegThreads)
+// Register budget: this kernel must become resident NEXT TO a GEMM CTA (6 warps x 160 registers;
+// the SM sub-partitions holding two of those warps have 16,384 - 10,240 = 6,144 registers left)
+// so that it — and, behind it, the next GEMM's CTAs — can start before the GEMM in front has
+// drained.  Two of its warps land on each sub-partition: <= 96 registers per thread.  At 101
+// registers the norm CTAs (and the GEMM CTAs queued behind them) only started once the previous
+// GEMM's CTAs had exited (tools/timeline.py).
+__global__ void __cluster_dims__(kNormSegments, 1, 1) __maxnreg__(96)
 add_rmsnorm_cluster_kernel(float* __restrict__ residual, const void* __restrict__ delta,
                            int delta_is_f32, int n_partials, long long partial_stride,
                            const float* __restrict__ w, __nv_bfloat16* __restrict__ xn,
@@ -193,10 +199,13 @@ add_rmsnorm_cluster_kernel(float* __restrict__ residual, const void* __restrict_
 #pragma unroll
     for (int i = 0; i < kSegThreads / 32; ++i) sg += red[i];
     seg_ss = sg;
+    BCG_TL(2, 4);
   }
   cluster.sync();
+  if (threadIdx.x == 0) BCG_TL(2, 5);
   if (threadIdx.x < kNormSegments) all_ss[threadIdx.x] = *cluster.map_shared_rank(&seg_ss, threadIdx.x);
   __syncthreads();
+  if (threadIdx.x == 0) BCG_TL(2, 6);
   cluster.barrier_arrive();  // my reads of the peers' seg_ss are done
   float tot = 0.f;
 #pragma unroll
@@ -208,6 +217,7 @@ add_rmsnorm_cluster_kernel(float* __restrict__ residual, const void* __restrict_
     if (threadIdx.x + i * kSegThreads < per && v < v_end)
       norm_store(residual, xn, !src_rows, static_cast<long long>(t) * d + v * 4, x[i], ww[i], inv);
   }
+  if (threadIdx.x == 0) BCG_TL(2, 7);
   cluster.barrier_wait();  // nobody leaves while a peer may still read its seg_ss
   if (threadIdx.x == 0) BCG_TL(2, 3);
 }
