@@ -88,8 +88,8 @@ embed_rmsnorm_kernel(const int* __restrict__ ids, const __nv_bfloat16* __restric
 //   * add_rmsnorm_cluster_kernel (T <= 128): a cluster of 8 CTAs x 256 threads per row, one
 //     segment per CTA, every load of a thread in flight at once, segment sums exchanged through
 //     distributed shared memory;
-//   * add_rmsnorm_row_kernel (prefill-sized T): one 1024-thread CTA per row, whose 32 warps play
-//     the 64 virtual warps in two turns.
+//   * add_rmsnorm_row_kernel (prefill-sized T): one 128-thread CTA per row, whose 4 warps play the
+//     64 virtual warps in turn.
 // Same order, same intrinsics -> bit-identical rows, so a row's result does not depend on how
 // many other rows share the launch (batch invariance across prefill and decode shapes).
 //
@@ -222,14 +222,20 @@ add_rmsnorm_cluster_kernel(float* __restrict__ residual, const void* __restrict_
   if (threadIdx.x == 0) BCG_TL(2, 3);
 }
 
-// One CTA per row; physical warp pw plays virtual warps pw and pw + 32 (see the order above).
-__global__ void __launch_bounds__(kNormThreads)
+// One 128-thread CTA per row (16 of them fit on an SM: the launch is bandwidth-bound, where the
+// earlier 1024-thread version reached a third of the HBM rate).  Physical warp pw plays the
+// virtual warps pw, pw + 4, ... of the order described above; the summed row is staged in shared
+// memory between the statistics pass and the scaling pass.
+constexpr int kRowThreads = 128;
+
+__global__ void __launch_bounds__(kRowThreads)
 add_rmsnorm_row_kernel(float* __restrict__ residual, const void* __restrict__ delta, int delta_is_f32,
                        int n_partials, long long partial_stride, const float* __restrict__ w,
                        __nv_bfloat16* __restrict__ xn, const int* __restrict__ src_rows, int d,
                        float eps) {
   constexpr int kVirtWarps = kNormSegments * kSegThreads / 32;  // 64
-  constexpr int kRounds = kVirtWarps / (kNormThreads / 32);     // 2
+  constexpr int kPhysWarps = kRowThreads / 32;                  // 4
+  extern __shared__ float4 row_stage[];                         // [d / 4]
   __shared__ float red[kVirtWarps];
   pdl_launch_dependents();
   pdl_wait();
@@ -238,24 +244,24 @@ add_rmsnorm_row_kernel(float* __restrict__ residual, const void* __restrict__ de
   const int nvec = d >> 2;
   const int per = (nvec + kNormSegments - 1) / kNormSegments;
   const int pw = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float4 x[kRounds][kSegTurns];
-#pragma unroll
-  for (int r = 0; r < kRounds; ++r) {
-    const int vw = pw + r * (kNormThreads / 32);
+  for (int vw = pw; vw < kVirtWarps; vw += kPhysWarps) {
     const int seg = vw >> 3;
     const int vt = (vw & 7) * 32 + lane;
-    const int v_end = min(nvec, (seg + 1) * per);
     float ss = 0.f;
+    if ((vw & 7) * 32 < per) {  // virtual warps past the segment's end contribute exact zeros
+      const int v_end = min(nvec, (seg + 1) * per);
 #pragma unroll
-    for (int i = 0; i < kSegTurns; ++i) {
-      const int v = seg * per + vt + i * kSegThreads;
-      if (vt + i * kSegThreads < per && v < v_end) {
-        x[r][i] = residual_plus_delta<kMaxPartialsBatch>(residual, delta, delta_is_f32, n_partials,
-                                                         partial_stride, src * d + v * 4);
-        ss = __fadd_rn(ss, sumsq4(x[r][i]));
+      for (int i = 0; i < kSegTurns; ++i) {
+        const int v = seg * per + vt + i * kSegThreads;
+        if (vt + i * kSegThreads < per && v < v_end) {
+          const float4 x = residual_plus_delta<4>(residual, delta, delta_is_f32, n_partials,
+                                                  partial_stride, src * d + v * 4);
+          row_stage[v] = x;
+          ss = __fadd_rn(ss, sumsq4(x));
+        }
       }
+      ss = warp_sum(ss);
     }
-    ss = warp_sum(ss);
     if (lane == 0) red[vw] = ss;
   }
   __syncthreads();
@@ -268,20 +274,10 @@ add_rmsnorm_row_kernel(float* __restrict__ residual, const void* __restrict__ de
     tot += sg;
   }
   const float inv = rsqrtf(tot / static_cast<float>(d) + eps);
-#pragma unroll
-  for (int r = 0; r < kRounds; ++r) {
-    const int vw = pw + r * (kNormThreads / 32);
-    const int seg = vw >> 3;
-    const int vt = (vw & 7) * 32 + lane;
-    const int v_end = min(nvec, (seg + 1) * per);
-#pragma unroll
-    for (int i = 0; i < kSegTurns; ++i) {
-      const int v = seg * per + vt + i * kSegThreads;
-      if (vt + i * kSegThreads < per && v < v_end) {
-        const float4 ww = *reinterpret_cast<const float4*>(w + v * 4);
-        norm_store(residual, xn, !src_rows, static_cast<long long>(t) * d + v * 4, x[r][i], ww, inv);
-      }
-    }
+  for (int v = threadIdx.x; v < nvec; v += kRowThreads) {
+    const float4 x = row_stage[v];
+    const float4 ww = *reinterpret_cast<const float4*>(w + v * 4);
+    norm_store(residual, xn, !src_rows, static_cast<long long>(t) * d + v * 4, x, ww, inv);
   }
 }
 
@@ -413,8 +409,14 @@ int add_rmsnorm(float* residual, const void* delta, int delta_is_f32, int n_part
                             stream, residual, delta, delta_is_f32, n_partials, partial_stride, w,
                             reinterpret_cast<__nv_bfloat16*>(xn), src_rows, d, eps));
   } else {
-    BCG_CUDA_CHECK(launch_k(add_rmsnorm_row_kernel, dim3(T), dim3(kNormThreads), 0, stream, residual,
-                            delta, delta_is_f32, n_partials, partial_stride, w,
+    static bool configured = false;
+    if (!configured) {
+      BCG_CUDA_CHECK(cudaFuncSetAttribute(add_rmsnorm_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          kNormSegments * kSegThreads * kSegTurns * 16));
+      configured = true;
+    }
+    BCG_CUDA_CHECK(launch_k(add_rmsnorm_row_kernel, dim3(T), dim3(kRowThreads), static_cast<size_t>(d) * 4,
+                            stream, residual, delta, delta_is_f32, n_partials, partial_stride, w,
                             reinterpret_cast<__nv_bfloat16*>(xn), src_rows, d, eps));
   }
   return BCG_OK;
