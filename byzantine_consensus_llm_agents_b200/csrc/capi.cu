@@ -77,6 +77,13 @@ int bcg_add_rmsnorm(float* residual, const void* delta, int delta_is_f32, int n_
                      d, eps, S(stream));
 }
 
+int bcg_add_norm_stats(float* residual, const void* delta, int delta_is_f32, int n_partials,
+                       long long partial_stride, const float* w, void* xn, float* sumsq, int T, int d,
+                       void* stream) {
+  return add_norm_stats(residual, delta, delta_is_f32, n_partials, partial_stride, w, xn, sumsq, T, d,
+                        S(stream));
+}
+
 int bcg_qknorm_rope_kvwrite(const void* qkv, int qkv_is_f32, int n_partials,
                             long long partial_stride, long long ld_qkv, const float* q_norm_w,
                             const float* k_norm_w, const float* cos_sin, const int* positions,

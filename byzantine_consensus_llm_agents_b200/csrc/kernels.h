@@ -23,6 +23,9 @@ int make_tmap_bf16_sw128(CUtensorMap* m, const void* ptr, long long rows, long l
 
 int embed_rmsnorm(const int* ids, const void* embed, const float* w, float* residual, void* xn,
                   int T, int d, float eps, cudaStream_t stream);
+int add_norm_stats(float* residual, const void* delta, int delta_is_f32, int n_partials,
+                   long long partial_stride, const float* w, void* xn, float* sumsq, int T, int d,
+                   cudaStream_t stream);
 int add_rmsnorm(float* residual, const void* delta, int delta_is_f32, int n_partials,
                 long long partial_stride, const float* w, void* xn, const int* src_rows, int T,
                 int d, float eps, cudaStream_t stream);

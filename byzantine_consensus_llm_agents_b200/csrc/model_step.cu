@@ -145,9 +145,14 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
   // while HBM is saturated and costs 7-10 us, the stand-alone norm 4-5 us on an idle memory system.
   const bool nf = tp == 1 && ws->row_sumsq && ws->tile_counters && (d % 128) == 0 && s_o <= 16 &&
                   s_dn <= 16 && (flags & BCG_STEP_FUSED_NORM) && !skip_norm;
-  const int n_tiles_d = d / 128;
-  float* sumsq_attn = ws->row_sumsq;                      // written by o, read by gate_up
-  float* sumsq_mlp = ws->row_sumsq ? ws->row_sumsq + static_cast<long long>(n_tiles_d) * 128 : nullptr;  // down -> qkv / lm_head
+  // Deferred norm (single GPU, opt-in with BCG_STEP_DEFERRED_NORM): bcg_add_norm_stats finishes the
+  // residual and writes bf16(residual * w) + 8 segment sums per row; the projection that follows
+  // applies 1/RMS in its epilogue, so the row-wide reduction leaves the critical path.
+  const bool dn = !nf && tp == 1 && ws->row_sumsq && B <= 128 && (flags & BCG_STEP_DEFERRED_NORM) && !skip_norm;
+  const int n_tiles_d = dn ? 8 : d / 128;
+  const int table_floats = (d / 128 > 8 ? d / 128 : 8) * 128;
+  float* sumsq_attn = ws->row_sumsq;                      // written after o, read by gate_up
+  float* sumsq_mlp = ws->row_sumsq ? ws->row_sumsq + table_floats : nullptr;  // after down -> qkv / lm_head
   auto consumer = [&](const float* table) {
     bcg_gemm_fusion f = {};
     f.scale_sumsq = table;
@@ -170,6 +175,9 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
       BCG_TRY(embed_rmsnorm(ids, m->embed, m->ln1[0], ws->residual, ws->xn, B, d, m->rms_eps, st));
     } else if (nf) {
       // ws->xn and sumsq_mlp were produced by the previous layer's down projection
+    } else if (dn) {
+      BCG_TRY(add_norm_stats(ws->residual, P, 1, s_dn, static_cast<long long>(B) * d, m->ln1[l], ws->xn,
+                             sumsq_mlp, B, d, st));
     } else if (fused) {
       BCG_TRY(tp_add_rmsnorm(ws->residual, off_dn, s_dn, static_cast<long long>(B) * d, m->ln1[l], ws->xn, 1,
                              B, d, m->rms_eps, st));
@@ -180,7 +188,7 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
     if (!skip_qkv) {
       const bcg_gemm_fusion f = consumer(sumsq_mlp);
       BCG_TRY(gemm_bf16_tn_fused(ws->xn, m->w_qkv[l], P, B, qkv_dim, d, d, d, qkv_dim, BCG_EPI_F32, s_qkv,
-                                 gf, (nf && l > 0) ? &f : nullptr, st));
+                                 gf, ((nf || dn) && l > 0) ? &f : nullptr, st));
     }
     if (!skip_rope)
     BCG_TRY(qknorm_rope_kvwrite(P, 1, s_qkv, static_cast<long long>(B) * qkv_dim, qkv_dim,
@@ -211,7 +219,10 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
     // row-parallel projection: sum the split-K slabs over the ranks in place (slab s of every rank
     // adds up to slab s); the norm kernel then adds the slabs as usual
     if (tp > 1) BCG_TRY(tp_all_reduce_f32(P, static_cast<long long>(s_o) * B * d, st));
-    if (!skip_norm)
+    if (dn) {
+      BCG_TRY(add_norm_stats(ws->residual, P, 1, s_o, static_cast<long long>(B) * d, m->ln2[l], ws->xn,
+                             sumsq_attn, B, d, st));
+    } else if (!skip_norm)
     BCG_TRY(add_rmsnorm(ws->residual, P, 1, s_o, static_cast<long long>(B) * d, m->ln2[l], ws->xn,
                         nullptr, B, d, m->rms_eps, st));
     }
@@ -219,10 +230,10 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
     if (skip_gu) {
     } else if (s_gu == 1) {
       BCG_TRY(gemm_bf16_tn_fused(ws->xn, m->w_gate_up[l], ws->act, B, 2 * ff, d, d, d, ff, BCG_EPI_SWIGLU, 1,
-                                 gf, nf ? &f_gu : nullptr, st));
+                                 gf, (nf || dn) ? &f_gu : nullptr, st));
     } else {
       BCG_TRY(gemm_bf16_tn_fused(ws->xn, m->w_gate_up[l], P, B, 2 * ff, d, d, d, 2 * ff, BCG_EPI_F32, s_gu,
-                                 gf, nf ? &f_gu : nullptr, st));
+                                 gf, (nf || dn) ? &f_gu : nullptr, st));
       BCG_TRY(swiglu_reduce(P, s_gu, static_cast<long long>(B) * 2 * ff, ws->act, B, 2 * ff, st));
     }
     if (fused) {
@@ -242,6 +253,9 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
   }
   if (nf) {
     // ws->xn_last and sumsq_mlp come from the last layer's down projection
+  } else if (dn) {
+    BCG_TRY(add_norm_stats(ws->residual, P, 1, s_dn, static_cast<long long>(B) * d, m->final_norm,
+                           ws->xn_last, sumsq_mlp, B, d, st));
   } else if (fused) {
     BCG_TRY(tp_add_rmsnorm(ws->residual, off_dn, s_dn, static_cast<long long>(B) * d, m->final_norm,
                            ws->xn_last, 1, B, d, m->rms_eps, st));
@@ -256,7 +270,7 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
   } else if (!skip_lm) {
     const bcg_gemm_fusion f = consumer(sumsq_mlp);
     BCG_TRY(gemm_bf16_tn_fused(ws->xn_last, m->lm_head, ws->logits, B, m->vocab, d, d, d, m->vocab,
-                               BCG_EPI_F32, 1, gf, nf ? &f : nullptr, st));
+                               BCG_EPI_F32, 1, gf, (nf || dn) ? &f : nullptr, st));
   }
   return BCG_OK;
 }

@@ -101,7 +101,8 @@ constexpr int kNormSegments = 8;
 constexpr int kSegThreads = 256;
 constexpr int kSegTurns = 2;  // d <= 8 * 256 * 2 * 4 = 16384
 constexpr int kPartialsInFlight = 12;
-constexpr int kNormClusterMaxRows = 128;  // decode-sized launches take the cluster kernel
+constexpr int kNormClusterMaxRows = 128;
+constexpr int kNormStatsStride = 128;     // rows per segment entry of the deferred-scale table  // decode-sized launches take the cluster kernel
 
 __device__ __forceinline__ float sumsq4(const float4& x) {
   return __fmaf_rn(x.w, x.w, __fmaf_rn(x.z, x.z, __fmaf_rn(x.y, x.y, __fmul_rn(x.x, x.x))));
@@ -220,6 +221,52 @@ add_rmsnorm_cluster_kernel(float* __restrict__ residual, const void* __restrict_
   if (threadIdx.x == 0) BCG_TL(2, 7);
   cluster.barrier_wait();  // nobody leaves while a peer may still read its seg_ss
   if (threadIdx.x == 0) BCG_TL(2, 3);
+}
+
+// Deferred-scale variant (decode): the residual add and bf16(r * w) are elementwise, only 1/RMS
+// needs the whole row — and the projection that consumes the activations can apply it in its
+// epilogue (bcg_gemm_bf16_tn_fused, consumer half).  So this kernel stops after the segment sums:
+// no cluster barrier, no DSMEM exchange on the critical path between two GEMMs.  It writes the
+// residual, xn = bf16(r * w) and sumsq[segment][row] (8 segments, stride 128 rows); the segment
+// sums are formed exactly as in the two kernels above.
+__global__ void __maxnreg__(96)
+add_norm_stats_kernel(float* __restrict__ residual, const void* __restrict__ delta, int delta_is_f32,
+                      int n_partials, long long partial_stride, const float* __restrict__ w,
+                      __nv_bfloat16* __restrict__ xn, float* __restrict__ sumsq, int d) {
+  __shared__ float red[kSegThreads / 32];
+  pdl_launch_dependents();
+  if (threadIdx.x == 0) BCG_TL(2, 0);
+  pdl_wait();
+  if (threadIdx.x == 0) BCG_TL(2, 1);
+  const int seg = blockIdx.x;
+  const int t = blockIdx.y;
+  const int nvec = d >> 2;
+  const int per = (nvec + kNormSegments - 1) / kNormSegments;
+  const int v_end = min(nvec, (seg + 1) * per);
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < kSegTurns; ++i) {
+    const int v = seg * per + threadIdx.x + i * kSegThreads;
+    if (threadIdx.x + i * kSegThreads < per && v < v_end) {
+      const long long off = static_cast<long long>(t) * d + v * 4;
+      const float4 ww = *reinterpret_cast<const float4*>(w + v * 4);
+      const float4 x = residual_plus_delta<kPartialsInFlight>(residual, delta, delta_is_f32, n_partials,
+                                                              partial_stride, off);
+      ss = __fadd_rn(ss, sumsq4(x));
+      *reinterpret_cast<float4*>(residual + off) = x;
+      store_bf16x4(xn + off, x.x * ww.x, x.y * ww.y, x.z * ww.z, x.w * ww.w);
+    }
+  }
+  ss = warp_sum(ss);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float sg = 0.f;
+#pragma unroll
+    for (int i = 0; i < kSegThreads / 32; ++i) sg += red[i];
+    sumsq[seg * kNormStatsStride + t] = sg;
+    BCG_TL(2, 3);
+  }
 }
 
 // One 128-thread CTA per row (16 of them fit on an SM: the launch is bandwidth-bound, where the
@@ -419,6 +466,20 @@ int add_rmsnorm(float* residual, const void* delta, int delta_is_f32, int n_part
                             stream, residual, delta, delta_is_f32, n_partials, partial_stride, w,
                             reinterpret_cast<__nv_bfloat16*>(xn), src_rows, d, eps));
   }
+  return BCG_OK;
+}
+
+int add_norm_stats(float* residual, const void* delta, int delta_is_f32, int n_partials,
+                   long long partial_stride, const float* w, void* xn, float* sumsq, int T, int d,
+                   cudaStream_t stream) {
+  if (!residual || !w || !xn || !sumsq || T <= 0 || T > kNormStatsStride || d <= 0 || (d % 4) ||
+      d > kNormSegments * kSegThreads * kSegTurns * 4 || n_partials < 1) {
+    set_last_error("bcg_add_norm_stats", "bad argument (T <= 128, d a multiple of 4 and <= 16384)");
+    return BCG_ERR_ARG;
+  }
+  BCG_CUDA_CHECK(launch_k(add_norm_stats_kernel, dim3(kNormSegments, T), dim3(kSegThreads), 0, stream,
+                          residual, delta, delta_is_f32, n_partials, partial_stride, w,
+                          reinterpret_cast<__nv_bfloat16*>(xn), sumsq, d));
   return BCG_OK;
 }
 

@@ -146,7 +146,7 @@ class Engine:
                  max_rows: int = 64, prefill_tokens: int = 16384, kv_pages: Optional[int] = None,
                  gpu_memory_utilization: float = 0.9, base_seed: int = 0, device: str = "cuda:0",
                  enable_prefix_cache: bool = True, use_cuda_graph: bool = True, pdl: bool = False,
-                 fused_norm: bool = False,
+                 fused_norm: bool = False, deferred_norm: Optional[bool] = None,
                  tp_rank: int = 0, tp_size: int = 1, tp_fused_allreduce: bool = True, tp_group=None):
         """`cfg` is the FULL architecture; with tp_size > 1 `weights` must be this rank's shard
         (Weights.shard / random_init_sharded) and bcg_tp_init must have been called (collective)."""
@@ -169,7 +169,13 @@ class Engine:
         self.calls = 0
         self.enable_prefix_cache = enable_prefix_cache
         self.use_cuda_graph = use_cuda_graph
-        self.flags = (L.GEMM_PDL if pdl else 0) | (L.STEP_FUSED_NORM if fused_norm else 0)
+        # How decode runs the residual add + RMSNorm between projections (include/bcg_b200.h,
+        # bcg_model_decode).  Default on one GPU: statistics kernel + 1/RMS in the next GEMM's epilogue
+        # (1.5 % faster per step than the complete norm kernel); TP engines keep the reduce+norm kernels.
+        if deferred_norm is None:
+            deferred_norm = tp_size == 1 and not fused_norm
+        self.flags = ((L.GEMM_PDL if pdl else 0) | (L.STEP_FUSED_NORM if fused_norm else 0)
+                      | (L.STEP_DEFERRED_NORM if deferred_norm else 0))
         self.max_blocks = (self.max_model_len + PAGE - 1) // PAGE
         self.max_steps = self.max_model_len
 
@@ -189,7 +195,7 @@ class Engine:
             so=z(B * lc.n_heads * self.max_splits_cap * 128, dt=f32),
             sml=z(B * lc.n_heads * self.max_splits_cap * 2, dt=f32),
             attn_counters=z(B * lc.n_kv_heads, dt=i32),
-            row_sumsq=z(2 * ((d + 127) // 128) * 128, dt=f32), tile_counters=z((d + 127) // 128, dt=i32),
+            row_sumsq=z(2 * max((d + 127) // 128, 8) * 128, dt=f32), tile_counters=z((d + 127) // 128, dt=i32),
             logits=z(B, full_cfg.vocab, dt=f32), xn_last=z(B, d))
         if tp_size > 1:
             self.buf["logits_local"] = z(B, lc.vocab, dt=f32)

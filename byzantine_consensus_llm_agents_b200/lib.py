@@ -15,6 +15,7 @@ LIB_PATH = PKG / "_lib" / "libbcg_b200.so"
 EPI_BF16, EPI_F32, EPI_SWIGLU = 0, 1, 2
 GEMM_PDL = 1
 STEP_FUSED_NORM = 0x20000   # bcg_model_decode: fold add+RMSNorm into the GEMMs (opt-in, slower)
+STEP_DEFERRED_NORM = 0x40000  # bcg_model_decode: norm statistics kernel + 1/RMS in the next GEMM's epilogue
 
 c_int_p = C.POINTER(C.c_int)
 c_float_p = C.POINTER(C.c_float)
@@ -86,6 +87,7 @@ _SIGS = {
     "bcg_embed_rmsnorm": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, vp]),
     "bcg_add_rmsnorm": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_longlong, vp, vp, vp, C.c_int,
                                   C.c_int, C.c_float, vp]),
+    "bcg_add_norm_stats": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_longlong, vp, vp, vp, C.c_int, C.c_int, vp]),
     "bcg_qknorm_rope_kvwrite": (C.c_int, [vp, C.c_int, C.c_int, C.c_longlong, C.c_longlong, vp, vp,
                                           vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int,
                                           C.c_float, vp]),

@@ -95,6 +95,17 @@ int bcg_add_rmsnorm(float* residual, const void* delta, int delta_is_f32, int n_
                     long long partial_stride, const float* w, void* xn, const int* src_rows, int T,
                     int d, float eps, void* stream);
 
+/* Decode-only variant of bcg_add_rmsnorm with the 1/RMS factor deferred to the consuming GEMM:
+ * residual += delta (same operand rules), xn = bf16(residual * w) — NOT divided by the RMS — and
+ * sumsq[s * 128 + t] = sum of squares of segment s (of 8) of row t.  Pass `sumsq` as
+ * bcg_gemm_fusion.scale_sumsq with scale_tiles = 8, scale_d = d to the projection that reads xn.
+ * T <= 128.  Takes the row-wide reduction (a cluster barrier and a DSMEM exchange in
+ * bcg_add_rmsnorm) off the critical path between two GEMMs.  Stands in for the same vllm op,
+ * `_C.fused_add_rms_norm`, with its last multiply moved into the next projection. */
+int bcg_add_norm_stats(float* residual, const void* delta, int delta_is_f32, int n_partials,
+                       long long partial_stride, const float* w, void* xn, float* sumsq, int T, int d,
+                       void* stream);
+
 /* Per-head q/k RMSNorm (weights may be NULL: Mistral), rotate-half RoPE from a
  * [max_pos][128] fp32 table (cos[0..63] | sin[0..63]), q -> bf16 [T, n_heads*128], k/v ->
  * paged cache at slot_map[t] (slot = page*page_size + offset; negative = skip).
@@ -265,7 +276,7 @@ typedef struct bcg_workspace {
   void* xn_last;      /* bf16 [B_max, d_model] */
   int T_max, B_max;
   /* decode norm fusion (bcg_gemm_bf16_tn_fused); both NULL = separate add_rmsnorm kernels */
-  float* row_sumsq;   /* fp32 [2][d_model/128][128]: per-tile row sums of squares, one table per norm */
+  float* row_sumsq;   /* fp32 [2][max(d_model/128, 8)][128]: row sums of squares per tile / segment, one table per norm */
   int* tile_counters; /* int32 [d_model/128], zero-initialised once */
 } bcg_workspace;
 
@@ -278,11 +289,14 @@ int bcg_model_prefill(const bcg_model* m, const bcg_workspace* ws, const int* id
                       const int* last_rows, int n_seqs, int T, void* stream);
 /* One decode step for B rows: ids/positions/slot_map/seq_lens are the arrays bcg_mask_sample
  * maintains; logits land in ws->logits[0..B).  Stands in for one decode step of the same vLLM
- * forward.  flags: BCG_GEMM_PDL; BCG_STEP_FUSED_NORM folds the residual add +
- * RMSNorm into the projections around it (bcg_gemm_bf16_tn_fused; needs ws->row_sumsq and
- * ws->tile_counters, single GPU).  Off by default: measured slower than the separate cluster
- * kernel. */
+ * forward.  flags: BCG_GEMM_PDL, plus how the residual add + RMSNorm between two
+ * projections is executed on a single GPU (both variants need ws->row_sumsq / ws->tile_counters):
+ *   default                   bcg_add_rmsnorm kernels (complete norm, then the projection)
+ *   BCG_STEP_DEFERRED_NORM    bcg_add_norm_stats + 1/RMS applied in the next projection's epilogue
+ *   BCG_STEP_FUSED_NORM       the producing projection finishes the residual itself
+ *                             (bcg_gemm_bf16_tn_fused producer half; measured slower) */
 #define BCG_STEP_FUSED_NORM 0x20000
+#define BCG_STEP_DEFERRED_NORM 0x40000
 int bcg_model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids,
                      const int* positions, const int* slot_map, const int* seq_lens,
                      const int* block_table, int max_blocks_per_seq, int B, int flags,

@@ -326,6 +326,47 @@ def test_add_rmsnorm_row_is_independent_of_launch_size(d, parts):
     assert torch.equal(xn_m[pick].view(torch.int16), xn_f.view(torch.int16))
 
 
+@pytest.mark.parametrize("T,d,parts", [(10, 5120, 11), (1, 256, 1), (128, 1024, 3), (7, 6144, 0), (5, 1000, 2)])
+def test_add_norm_stats_plus_consumer_scale_equals_add_rmsnorm(T, d, parts):
+    """bcg_add_norm_stats leaves the residual exactly as bcg_add_rmsnorm does, xn = bf16(r*w), and
+    segment sums from which the consuming GEMM's epilogue rebuilds 1/RMS."""
+    import ctypes as C
+    lib = _lib()
+    res0 = torch.randn(T, d, device=DEV)
+    w = (torch.rand(d, device=DEV) + 0.5).float()
+    if parts == 0:
+        delta, is_f32, n = _rand_bf16(T, d, seed=51), 0, 1
+    else:
+        delta, is_f32, n = torch.randn(parts, T, d, device=DEV), 1, parts
+    res_a, res_b = res0.clone(), res0.clone()
+    xn_a = torch.empty(T, d, device=DEV, dtype=torch.bfloat16)
+    xn_b = torch.empty(T, d, device=DEV, dtype=torch.bfloat16)
+    sumsq = torch.full((8, 128), float("nan"), device=DEV)
+    L.check(lib.bcg_add_rmsnorm(res_a.data_ptr(), delta.data_ptr(), is_f32, n, T * d, w.data_ptr(),
+                                xn_a.data_ptr(), None, T, d, 1e-6, L.stream_ptr()))
+    L.check(lib.bcg_add_norm_stats(res_b.data_ptr(), delta.data_ptr(), is_f32, n, T * d, w.data_ptr(),
+                                   xn_b.data_ptr(), sumsq.data_ptr(), T, d, L.stream_ptr()))
+    torch.cuda.synchronize()
+    assert torch.equal(res_a, res_b)
+    assert torch.equal(xn_b, (res_b * w).to(torch.bfloat16))
+    tot = sumsq[:, :T].sum(0)
+    assert torch.allclose(tot, res_b.pow(2).sum(-1), rtol=1e-5)
+    # a projection fed with xn_b and the table reproduces the projection of the normalised row
+    if d % 8 == 0:
+        N = 256
+        wt = _rand_bf16(N, d, scale=0.05, seed=52)
+        f = _fusion(scale_sumsq=sumsq, scale_tiles=8, scale_d=d, scale_eps=1e-6)
+        got = torch.zeros(T, N, device=DEV)
+        L.check(lib.bcg_gemm_bf16_tn_fused(xn_b.data_ptr(), wt.data_ptr(), got.data_ptr(), T, N, d, d, d, N,
+                                           L.EPI_F32, 1, 0, C.byref(f), L.stream_ptr()))
+        ref = torch.zeros(T, N, device=DEV)
+        L.gemm(xn_a, wt, ref, L.EPI_F32)
+        torch.cuda.synchronize()
+        assert ((got - ref).abs() <= ref.abs() * 2 ** -6 + 2e-2 * ref.abs().mean()).all()
+    assert lib.bcg_add_norm_stats(res_b.data_ptr(), delta.data_ptr(), is_f32, n, T * d, w.data_ptr(),
+                                  xn_b.data_ptr(), sumsq.data_ptr(), 129, d, L.stream_ptr()) != 0
+
+
 def test_add_rmsnorm_gather_rows():
     lib = _lib()
     T, d, n = 50, 1024, 4

@@ -73,12 +73,15 @@ def test_logits_match_fp32_cpu_forward(cfg, tol):
     print(f"{cfg.name}: worst |dlogit| = {worst:.4f}")
 
 
+@pytest.mark.parametrize("mode", [{"fused_norm": True}, {"deferred_norm": False}, {"deferred_norm": True}],
+                         ids=["fused", "complete", "deferred"])
 @pytest.mark.parametrize("cfg", [TINY_QWEN, TINY_MISTRAL], ids=lambda c: c.name)
-def test_fused_norm_decode_path_matches_fp32_forward(cfg):
-    """Opt-in decode variant with the residual add + RMSNorm folded into the GEMMs
-    (bcg_gemm_bf16_tn_fused): same tolerance against the fp32 CPU forward, and the same greedy
-    tokens as the default path wherever the fp32 margin is clear."""
-    hf, eng, tk = _setup(cfg, fused_norm=True, pdl=True)
+def test_every_norm_decode_path_matches_fp32_forward(cfg, mode):
+    """The three ways decode can run the residual add + RMSNorm between projections: statistics
+    kernel with 1/RMS applied in the next GEMM's epilogue (the single-GPU default), the complete
+    norm kernel (what TP engines use), and the norm folded into the producing GEMM (opt-in).  Same
+    tolerance against the fp32 CPU forward for each."""
+    hf, eng, tk = _setup(cfg, pdl=True, **mode)
     rng = np.random.default_rng(0)
     lens = [5, 64, 200]
     n_new = 10
