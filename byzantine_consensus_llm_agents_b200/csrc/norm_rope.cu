@@ -341,24 +341,61 @@ qknorm_rope_kvwrite_kernel(const void* __restrict__ qkv, int qkv_is_f32, int n_p
                            int page_size, float eps) {
   pdl_launch_dependents();
   if (threadIdx.x == 0) BCG_TL(3, 0);
-  pdl_wait();
-  if (threadIdx.x == 0) BCG_TL(3, 1);
   const int lane = threadIdx.x & 31;
   const int heads_total = n_heads + 2 * n_kv_heads;
   const long long wid = static_cast<long long>(blockIdx.x) * 4 + (threadIdx.x >> 5);
-  if (wid < static_cast<long long>(T) * heads_total) {
-    const int t = static_cast<int>(wid / heads_total);
-    const int h = static_cast<int>(wid - static_cast<long long>(t) * heads_total);
+  const bool live = wid < static_cast<long long>(T) * heads_total;
+  const int t = live ? static_cast<int>(wid / heads_total) : 0;
+  const int h = live ? static_cast<int>(wid - static_cast<long long>(t) * heads_total) : 0;
+  const bool is_q = h < n_heads;
+  const bool is_k = !is_q && h < n_heads + n_kv_heads;
+  // Everything that does not come from the GEMM in front is fetched BEFORE the dependency wait:
+  // position, cache slot (written by the previous step's sampler, which never triggers its
+  // dependents early), the RoPE table row and the norm weights.
+  const float* nw = is_q ? q_norm_w : (is_k ? k_norm_w : nullptr);
+  float2 wl = make_float2(1.f, 1.f), wh = make_float2(1.f, 1.f), c = make_float2(1.f, 1.f),
+         sn = make_float2(0.f, 0.f);
+  int slot = -1;
+  if (live) {
+    if (nw) {
+      wl = *reinterpret_cast<const float2*>(nw + 2 * lane);
+      wh = *reinterpret_cast<const float2*>(nw + 64 + 2 * lane);
+    }
+    if (is_q || is_k) {
+      const int pos = positions[t];
+      c = *reinterpret_cast<const float2*>(cos_sin + static_cast<long long>(pos) * 128 + 2 * lane);
+      sn = *reinterpret_cast<const float2*>(cos_sin + static_cast<long long>(pos) * 128 + 64 + 2 * lane);
+    }
+    if (!is_q) slot = slot_map[t];
+  }
+  pdl_wait();
+  if (threadIdx.x == 0) BCG_TL(3, 1);
+  if (live) {
     const long long base = static_cast<long long>(t) * ld_qkv + h * 128;
     float lo0, lo1, hi0, hi1;
     if (qkv_is_f32) {
       const float* p = reinterpret_cast<const float*>(qkv) + base;
-      float2 a = *reinterpret_cast<const float2*>(p + 2 * lane);
-      float2 b = *reinterpret_cast<const float2*>(p + 64 + 2 * lane);
-      for (int s = 1; s < n_partials; ++s) {
-        const float2 a2 = *reinterpret_cast<const float2*>(p + s * partial_stride + 2 * lane);
-        const float2 b2 = *reinterpret_cast<const float2*>(p + s * partial_stride + 64 + 2 * lane);
-        a.x += a2.x; a.y += a2.y; b.x += b2.x; b.y += b2.y;
+      // slabs are requested eight at a time, unconditionally (indices past the end re-read the last
+      // slab and are ignored), and added in index order
+      float2 a = make_float2(0.f, 0.f), b = make_float2(0.f, 0.f);
+      for (int s0 = 0; s0 < n_partials; s0 += 8) {
+        float2 pa[8], pb[8];
+#pragma unroll
+        for (int s = 0; s < 8; ++s) {
+          const long long so = static_cast<long long>(min(s0 + s, n_partials - 1)) * partial_stride;
+          pa[s] = *reinterpret_cast<const float2*>(p + so + 2 * lane);
+          pb[s] = *reinterpret_cast<const float2*>(p + so + 64 + 2 * lane);
+        }
+#pragma unroll
+        for (int s = 0; s < 8; ++s) {
+          if (s0 + s < n_partials) {
+            if (s0 + s == 0) {
+              a = pa[s]; b = pb[s];
+            } else {
+              a.x += pa[s].x; a.y += pa[s].y; b.x += pb[s].x; b.y += pb[s].y;
+            }
+          }
+        }
       }
       lo0 = a.x; lo1 = a.y; hi0 = b.x; hi1 = b.y;
     } else {
@@ -367,25 +404,17 @@ qknorm_rope_kvwrite_kernel(const void* __restrict__ qkv, int qkv_is_f32, int n_p
       const uint32_t b = *reinterpret_cast<const uint32_t*>(p + 64 + 2 * lane);
       lo0 = bf16lo(a); lo1 = bf16hi(a); hi0 = bf16lo(b); hi1 = bf16hi(b);
     }
-    const bool is_q = h < n_heads;
-    const bool is_k = !is_q && h < n_heads + n_kv_heads;
     if (is_q || is_k) {
-      const float* nw = is_q ? q_norm_w : k_norm_w;
       if (nw) {
         const float ss = warp_sum(lo0 * lo0 + lo1 * lo1 + hi0 * hi0 + hi1 * hi1);
         const float inv = rsqrtf(ss * (1.0f / 128.0f) + eps);
-        const float2 wl = *reinterpret_cast<const float2*>(nw + 2 * lane);
-        const float2 wh = *reinterpret_cast<const float2*>(nw + 64 + 2 * lane);
         lo0 = lo0 * inv * wl.x; lo1 = lo1 * inv * wl.y;
         hi0 = hi0 * inv * wh.x; hi1 = hi1 * inv * wh.y;
       }
-      const int pos = positions[t];
-      const float2 c = *reinterpret_cast<const float2*>(cos_sin + static_cast<long long>(pos) * 128 + 2 * lane);
-      const float2 s = *reinterpret_cast<const float2*>(cos_sin + static_cast<long long>(pos) * 128 + 64 + 2 * lane);
-      const float r_lo0 = lo0 * c.x - hi0 * s.x;
-      const float r_lo1 = lo1 * c.y - hi1 * s.y;
-      const float r_hi0 = hi0 * c.x + lo0 * s.x;
-      const float r_hi1 = hi1 * c.y + lo1 * s.y;
+      const float r_lo0 = lo0 * c.x - hi0 * sn.x;
+      const float r_lo1 = lo1 * c.y - hi1 * sn.y;
+      const float r_hi0 = hi0 * c.x + lo0 * sn.x;
+      const float r_hi1 = hi1 * c.y + lo1 * sn.y;
       lo0 = r_lo0; lo1 = r_lo1; hi0 = r_hi0; hi1 = r_hi1;
     }
     const uint32_t plo = pack_bf16(lo0, lo1), phi = pack_bf16(hi0, hi1);
@@ -395,7 +424,6 @@ qknorm_rope_kvwrite_kernel(const void* __restrict__ qkv, int qkv_is_f32, int n_p
       *reinterpret_cast<uint32_t*>(o + 64 + 2 * lane) = phi;
     } else {
       const int kvh = is_k ? h - n_heads : h - n_heads - n_kv_heads;
-      const int slot = slot_map[t];
       if (slot >= 0) {
         const int page = slot / page_size, off = slot - page * page_size;
         __nv_bfloat16* o = kv_cache +
@@ -419,10 +447,25 @@ swiglu_reduce_kernel(const float* __restrict__ partials, int n_partials, long lo
     const int j = static_cast<int>(i - t * f);
     const long long col = static_cast<long long>(j / 16) * 32 + (j % 16);
     const float* p = partials + t * (2LL * f) + col;
-    float g = p[0], u = p[16];
-    for (int s = 1; s < n_partials; ++s) {
-      g += p[s * partial_stride];
-      u += p[s * partial_stride + 16];
+    float g = 0.f, u = 0.f;
+    for (int s0 = 0; s0 < n_partials; s0 += 8) {  // eight slabs in flight, added in index order
+      float pg[8], pu[8];
+#pragma unroll
+      for (int s = 0; s < 8; ++s) {
+        const long long so = static_cast<long long>(min(s0 + s, n_partials - 1)) * partial_stride;
+        pg[s] = p[so];
+        pu[s] = p[so + 16];
+      }
+#pragma unroll
+      for (int s = 0; s < 8; ++s) {
+        if (s0 + s < n_partials) {
+          if (s0 + s == 0) {
+            g = pg[s]; u = pu[s];
+          } else {
+            g += pg[s]; u += pu[s];
+          }
+        }
+      }
     }
     act[i] = __float2bfloat16_rn(g * (1.0f / (1.0f + __expf(-g))) * u);
   }

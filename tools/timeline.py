@@ -107,7 +107,7 @@ def main():
         assert per * n_gemm == len(t), (p, len(t), n_gemm)
         gem[p] = t.reshape(n_gemm, per)
     have_norm = (2, 0) in ev
-    norm = {p: instances_by_gap(ev[(2, p)], 8000) for p in (0, 1, 3, 4, 5, 6, 7)} if have_norm else {0: []}
+    norm = {p: instances_by_gap(ev[(2, p)], 8000) for p in (0, 1, 3, 4, 5, 6, 7) if (2, p) in ev} if have_norm else {0: []}
     rope = {p: instances_by_gap(ev[(3, p)], 30000) for p in (0, 1)}
     att = {p: instances_by_gap(ev[(4, p)], 30000) for p in (0, 1, 2)}
     att_exit = instances_by_gap(np.concatenate([ev[(4, 3)], ev.get((4, 5), np.zeros(0, np.int64))]), 30000)
@@ -144,10 +144,11 @@ def main():
             if nm == "o" and have_norm:
                 e["normB entry"] = norm[0][2 * l].min()
                 e["normB past wait first/last"] = (norm[1][2 * l].min(), norm[1][2 * l].max())
-                e["normB loads+block sum done first/last"] = (norm[4][2 * l].min(), norm[4][2 * l].max())
-                e["normB cluster.sync passed first/last"] = (norm[5][2 * l].min(), norm[5][2 * l].max())
-                e["normB DSMEM read done first/last"] = (norm[6][2 * l].min(), norm[6][2 * l].max())
-                e["normB stores issued first/last"] = (norm[7][2 * l].min(), norm[7][2 * l].max())
+                if 4 in norm:  # the complete (cluster) norm stamps its phases; the statistics kernel does not
+                    e["normB loads+block sum done first/last"] = (norm[4][2 * l].min(), norm[4][2 * l].max())
+                    e["normB cluster.sync passed first/last"] = (norm[5][2 * l].min(), norm[5][2 * l].max())
+                    e["normB DSMEM read done first/last"] = (norm[6][2 * l].min(), norm[6][2 * l].max())
+                    e["normB stores issued first/last"] = (norm[7][2 * l].min(), norm[7][2 * l].max())
                 e["normB exit (last CTA)"] = norm[3][2 * l].max()
         rows.append({k: (np.array(v) - t0) for k, v in e.items()})
     print(f"average over layers {layers.start}..{layers.stop - 1}, us relative to the qkv GEMM passing its wait:")
