@@ -513,7 +513,9 @@ def _attn_ref(q, K, V, G, causal_pos=None):
 
 @pytest.mark.parametrize("H,HKV,lens", [(4, 2, [1, 16, 17, 300]), (40, 8, [2000, 1700, 5, 256, 257]),
                                         (16, 8, [1023, 1024, 1025]), (32, 8, [700, 3]),
-                                        (48, 8, [513]), (64, 8, [100, 900])])
+                                        (48, 8, [513]), (64, 8, [100, 900]),
+                                        # more than 8 chunks per row: the merge's long-row branch
+                                        (8, 2, [4100, 2049, 300, 2048]), (40, 8, [8000])])
 def test_decode_attn_paged(H, HKV, lens):
     lib = _lib()
     B = len(lens)
