@@ -30,6 +30,7 @@ def main():
     ap.add_argument("--rows", type=int, default=10)
     ap.add_argument("--ctx", type=int, default=1600)
     ap.add_argument("--pdl", type=int, default=1)
+    ap.add_argument("--period-only", action="store_true", help="skip the per-kernel ablation")
     ap.add_argument("--base-flags", type=lambda x: int(x, 0), default=0,
                     help="extra bcg_model_decode flags for every run, e.g. 0x20000 = norm folded into the GEMMs")
     a = ap.parse_args()
@@ -81,6 +82,36 @@ def main():
           f"({nbytes / full / 1e6:.0f} GB/s = {100 * nbytes / full / 1e6 / peak:.1f} % of {peak} GB/s); "
           f"weights-only floor {cfg.decode_weight_bytes() / peak / 1e6:.3f} ms")
     out = {"full_ms": full}
+
+    # the real per-token period: decode step + sampler, k tokens per graph, graphs replayed back to back
+    def token_period(k, reps=24):
+        reset()
+        r["grammar_id"][:B] = -1
+        r["max_tokens"][:B] = 1 << 20
+        r["temperature"][:B] = 0.5
+        eng._decode_step(B, max_splits, False)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for _ in range(k):
+                eng._decode_step(B, max_splits, False)
+        g.replay()
+        torch.cuda.synchronize()
+        reset()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps // k):
+            g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / (reps // k * k)
+
+    for k in (1, 2, 4, 8):
+        out[f"token_period_ms_k{k}"] = token_period(k)
+        print(f"  step + sampler, {k} token(s) per graph, graphs back to back: {out[f'token_period_ms_k{k}']:.3f} ms per token")
+    if a.period_only:
+        print(json.dumps(out))
+        return
     for name, bit in SKIPS.items():
         t = time_step(bit)
         out[name] = full - t
