@@ -73,14 +73,36 @@ __device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
 //               whose probabilities it already holds in its S accumulators — and interleaves
 //               them pairwise (PRMT) into B fragments; output column g of n-tile j is head dim
 //               64(j>>3) + 8g + (j&7).
-template <int G>
+// FUSED variant (bcg_decode_attn_paged_qkv): the qk-norm / RoPE / KV-write kernel disappears.
+// Input is the qkv projection's raw split-K slabs.  Every chunk CTA rebuilds the queries of its
+// G heads itself (64 consumer threads, one round trip of slab loads, per-head RMSNorm by warp
+// reduction, rotate-half partner = lane ^ 16) and parks them in shared memory as bf16; the CTA of
+// the row's LAST chunk also builds the new token's K and V row (producer warp, the arithmetic of
+// qknorm_rope_kvwrite_kernel to the bit), writes it to the cache for later steps and patches it
+// into the page it has just streamed in — so that page, too, can be requested before the
+// dependency wait, and the wait is on the qkv GEMM instead of on a kernel behind it.
+struct RopeFusion {
+  const float* qkv;        // [n_partials][T, ld_qkv] fp32 split-K slabs: q heads | k heads | v heads
+  int n_partials;
+  long long partial_stride;
+  long long ld_qkv;
+  const float* q_norm_w;   // [128] or nullptr (no QK-norm)
+  const float* k_norm_w;
+  const float* cos_sin;    // [max_pos][128]: cos[0..63] | sin[0..63]
+  const int* positions;    // [B]
+  const int* slot_map;     // [B], negative = do not write the cache
+  __nv_bfloat16* kv_cache;
+  float eps;
+};
+
+template <int G, bool FUSED>
 __global__ void __launch_bounds__(kAttnThreads, 4)
 decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat16* __restrict__ q,
                    const int* __restrict__ block_table, int max_blocks,
                    const int* __restrict__ seq_lens, float* __restrict__ scratch_o,
                    float* __restrict__ scratch_ml, int* __restrict__ counters,
                    __nv_bfloat16* __restrict__ out, int n_heads, int n_kv_heads, int max_splits,
-                   float scale_log2e) {
+                   float scale_log2e, const RopeFusion rf) {
   extern __shared__ uint8_t attn_smem_raw[];
   uint8_t* ring = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(attn_smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
@@ -92,6 +114,8 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
   __shared__ float sm_m[kAttnConsumers][G];
   __shared__ float sm_l[kAttnConsumers][G];
   __shared__ int sm_last;
+  __shared__ uint64_t patch_bar;                      // FUSED: the newest token's K/V row is in place
+  __shared__ __align__(16) __nv_bfloat16 sm_q[G][128];  // FUSED: the CTA's queries
   pdl_launch_dependents();
   if (threadIdx.x == 0) BCG_TL(4, 0);
 
@@ -106,6 +130,7 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
     }
+    mbar_init(&patch_bar, 1);
     fence_barrier_init();
   }
   __syncthreads();
@@ -139,16 +164,110 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
     const int my_pg = split * (kSplitTokens / kPage) + lane;
     if (lane < kSplitTokens / kPage && my_pg < max_blocks)
       my_phys = block_table[static_cast<long long>(b) * max_blocks + my_pg];
-    n_pre = min(kAttnStages, n_pages - (split == n_splits - 1 ? 1 : 0));
+    // unfused: the row's last page waits for qknorm_rope_kvwrite; fused: it is patched below
+    n_pre = min(kAttnStages, n_pages - ((!FUSED && split == n_splits - 1) ? 1 : 0));
     for (int p = 0; p < n_pre; ++p) {
       const int phys = __shfl_sync(0xffffffffu, my_phys, p);
       if (lane == 0) issue_page(p, phys);
+    }
+  }
+  // FUSED: what the query / new-token math needs besides the GEMM's slabs is stable too
+  constexpr int kQSlots = (G * 32 + 63) / 64;  // float4 slots of the G x 128 queries per consumer thread
+  const bool last_chunk = live && split == n_splits - 1;
+  float4 qw[kQSlots], qcos, qsin;              // consumers: q-norm weights per slot, RoPE row
+  float2 kwl, kwh, kc, ks;                     // producer: k-norm weights and RoPE row (rope-kernel layout)
+  int new_slot = -1;
+  if constexpr (FUSED) {
+    if (live) {
+      const int pos = rf.positions[b];
+      const float* cs = rf.cos_sin + static_cast<long long>(pos) * 128;
+      if (warp != kAttnConsumers) {
+        const int d4 = threadIdx.x & 31;       // slot f = tid + 64 k  ->  head (tid >> 5) + 2 k, float4 d4
+        qcos = *reinterpret_cast<const float4*>(cs + (d4 & 15) * 4);
+        qsin = *reinterpret_cast<const float4*>(cs + 64 + (d4 & 15) * 4);
+#pragma unroll
+        for (int k = 0; k < kQSlots; ++k)
+          qw[k] = rf.q_norm_w ? *reinterpret_cast<const float4*>(rf.q_norm_w + d4 * 4)
+                              : make_float4(1.f, 1.f, 1.f, 1.f);
+      } else if (last_chunk) {
+        new_slot = rf.slot_map[b];
+        kc = *reinterpret_cast<const float2*>(cs + 2 * lane);
+        ks = *reinterpret_cast<const float2*>(cs + 64 + 2 * lane);
+        kwl = rf.k_norm_w ? *reinterpret_cast<const float2*>(rf.k_norm_w + 2 * lane) : make_float2(1.f, 1.f);
+        kwh = rf.k_norm_w ? *reinterpret_cast<const float2*>(rf.k_norm_w + 64 + 2 * lane) : make_float2(1.f, 1.f);
+      }
     }
   }
   pdl_wait();
   if (threadIdx.x == 0) BCG_TL(4, 1);
   if (!live) return;  // whole CTA
   uint32_t qa[8][2];
+  if constexpr (FUSED) {
+    if (warp != kAttnConsumers) {
+      // ---- queries: sum the slabs (index order), per-head RMSNorm, rotate-half RoPE, bf16 -> sm_q
+      const int d4 = threadIdx.x & 31;
+      const float* qrow = rf.qkv + static_cast<long long>(b) * rf.ld_qkv + static_cast<long long>(head0) * 128;
+      float4 x[kQSlots];
+#pragma unroll
+      for (int k = 0; k < kQSlots; ++k) x[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int s0 = 0; s0 < rf.n_partials; s0 += 6) {
+        float4 pp[kQSlots][6];
+#pragma unroll
+        for (int k = 0; k < kQSlots; ++k) {
+          const int hd = min((threadIdx.x >> 5) + 2 * k, G - 1);  // clamp: surplus slots re-read, unused
+#pragma unroll
+          for (int sp = 0; sp < 6; ++sp)
+            pp[k][sp] = *reinterpret_cast<const float4*>(
+                qrow + static_cast<long long>(min(s0 + sp, rf.n_partials - 1)) * rf.partial_stride + hd * 128 + d4 * 4);
+        }
+#pragma unroll
+        for (int k = 0; k < kQSlots; ++k) {
+#pragma unroll
+          for (int sp = 0; sp < 6; ++sp) {
+            if (s0 + sp < rf.n_partials) {
+              if (s0 + sp == 0) {
+                x[k] = pp[k][sp];
+              } else {
+                x[k].x += pp[k][sp].x; x[k].y += pp[k][sp].y; x[k].z += pp[k][sp].z; x[k].w += pp[k][sp].w;
+              }
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < kQSlots; ++k) {
+        const int hd = (threadIdx.x >> 5) + 2 * k;  // warp-uniform
+        if (hd < G) {
+          float4 v = x[k];
+          if (rf.q_norm_w) {
+            const float ss = warp_sum(v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w);
+            const float inv = rsqrtf(ss * (1.0f / 128.0f) + rf.eps);
+            v.x = v.x * inv * qw[k].x; v.y = v.y * inv * qw[k].y;
+            v.z = v.z * inv * qw[k].z; v.w = v.w * inv * qw[k].w;
+          }
+          // rotate-half partner (dim +-64) sits 16 lanes away
+          float4 o4;
+          o4.x = __shfl_xor_sync(0xffffffffu, v.x, 16);
+          o4.y = __shfl_xor_sync(0xffffffffu, v.y, 16);
+          o4.z = __shfl_xor_sync(0xffffffffu, v.z, 16);
+          o4.w = __shfl_xor_sync(0xffffffffu, v.w, 16);
+          float4 r;
+          if (d4 < 16) {  // low half: lo*cos - hi*sin
+            r.x = v.x * qcos.x - o4.x * qsin.x; r.y = v.y * qcos.y - o4.y * qsin.y;
+            r.z = v.z * qcos.z - o4.z * qsin.z; r.w = v.w * qcos.w - o4.w * qsin.w;
+          } else {        // high half: hi*cos + lo*sin
+            r.x = v.x * qcos.x + o4.x * qsin.x; r.y = v.y * qcos.y + o4.y * qsin.y;
+            r.z = v.z * qcos.z + o4.z * qsin.z; r.w = v.w * qcos.w + o4.w * qsin.w;
+          }
+          uint2 pk;
+          pk.x = pack_bf16(r.x, r.y);
+          pk.y = pack_bf16(r.z, r.w);
+          *reinterpret_cast<uint2*>(&sm_q[hd][d4 * 4]) = pk;
+        }
+      }
+      asm volatile("bar.sync 1, %0;" ::"n"(kAttnConsumers * 32) : "memory");
+    }
+  }
   if (warp != kAttnConsumers) {
     // Q as A fragments: [k-step][a0 (k 2t,2t+1), a2 (k 8+2t,9+2t)]; rows 8..15 (a1, a3) are zero
 #pragma unroll
@@ -156,7 +275,11 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
       uint4 raw = make_uint4(0u, 0u, 0u, 0u);
       if (g < G) {
         const int c = 2 * t + (j & 1) + 8 * (j >> 1);
-        raw = *reinterpret_cast<const uint4*>(q + (static_cast<long long>(b) * n_heads + head0 + g) * 128 + 8 * c);
+        if constexpr (FUSED) {
+          raw = *reinterpret_cast<const uint4*>(&sm_q[g][8 * c]);
+        } else {
+          raw = *reinterpret_cast<const uint4*>(q + (static_cast<long long>(b) * n_heads + head0 + g) * 128 + 8 * c);
+        }
       }
       qa[2 * j][0] = raw.x; qa[2 * j][1] = raw.y;
       qa[2 * j + 1][0] = raw.z; qa[2 * j + 1][1] = raw.w;
@@ -165,11 +288,84 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
 
   if (warp == kAttnConsumers) {
     // ------------------------------ TMA producer ------------------------------
+    uint32_t k_lo = 0, k_hi = 0, v_lo = 0, v_hi = 0;
+    if constexpr (FUSED) {
+      if (last_chunk) {
+        // the new token's K (norm + RoPE) and V row of this KV head — qknorm_rope_kvwrite_kernel's
+        // arithmetic and lane layout (dims 2l, 2l+1, 64+2l, 64+2l+1) to the bit
+        const float* krow = rf.qkv + static_cast<long long>(b) * rf.ld_qkv +
+                            static_cast<long long>(n_heads + kvh) * 128;
+        const float* vrow = krow + static_cast<long long>(n_kv_heads) * 128;
+        float2 ka = make_float2(0.f, 0.f), kb = ka, va = ka, vb = ka;
+        for (int s0 = 0; s0 < rf.n_partials; s0 += 8) {
+          float2 pka[8], pkb[8], pva[8], pvb[8];
+#pragma unroll
+          for (int sp = 0; sp < 8; ++sp) {
+            const long long so = static_cast<long long>(min(s0 + sp, rf.n_partials - 1)) * rf.partial_stride;
+            pka[sp] = *reinterpret_cast<const float2*>(krow + so + 2 * lane);
+            pkb[sp] = *reinterpret_cast<const float2*>(krow + so + 64 + 2 * lane);
+            pva[sp] = *reinterpret_cast<const float2*>(vrow + so + 2 * lane);
+            pvb[sp] = *reinterpret_cast<const float2*>(vrow + so + 64 + 2 * lane);
+          }
+#pragma unroll
+          for (int sp = 0; sp < 8; ++sp) {
+            if (s0 + sp < rf.n_partials) {
+              if (s0 + sp == 0) {
+                ka = pka[sp]; kb = pkb[sp]; va = pva[sp]; vb = pvb[sp];
+              } else {
+                ka.x += pka[sp].x; ka.y += pka[sp].y; kb.x += pkb[sp].x; kb.y += pkb[sp].y;
+                va.x += pva[sp].x; va.y += pva[sp].y; vb.x += pvb[sp].x; vb.y += pvb[sp].y;
+              }
+            }
+          }
+        }
+        float lo0 = ka.x, lo1 = ka.y, hi0 = kb.x, hi1 = kb.y;
+        if (rf.k_norm_w) {
+          const float ss = warp_sum(lo0 * lo0 + lo1 * lo1 + hi0 * hi0 + hi1 * hi1);
+          const float inv = rsqrtf(ss * (1.0f / 128.0f) + rf.eps);
+          lo0 = lo0 * inv * kwl.x; lo1 = lo1 * inv * kwl.y;
+          hi0 = hi0 * inv * kwh.x; hi1 = hi1 * inv * kwh.y;
+        }
+        const float r_lo0 = lo0 * kc.x - hi0 * ks.x;
+        const float r_lo1 = lo1 * kc.y - hi1 * ks.y;
+        const float r_hi0 = hi0 * kc.x + lo0 * ks.x;
+        const float r_hi1 = hi1 * kc.y + lo1 * ks.y;
+        k_lo = pack_bf16(r_lo0, r_lo1); k_hi = pack_bf16(r_hi0, r_hi1);
+        v_lo = pack_bf16(va.x, va.y); v_hi = pack_bf16(vb.x, vb.y);
+        if (new_slot >= 0) {  // for the steps to come
+          const int page = new_slot / kPage, off = new_slot - page * kPage;
+          __nv_bfloat16* kd = rf.kv_cache + ((static_cast<long long>(page) * 2 * n_kv_heads + kvh) * kPage + off) * 128;
+          __nv_bfloat16* vd = kd + static_cast<long long>(n_kv_heads) * kPage * 128;
+          *reinterpret_cast<uint32_t*>(kd + 2 * lane) = k_lo;
+          *reinterpret_cast<uint32_t*>(kd + 64 + 2 * lane) = k_hi;
+          *reinterpret_cast<uint32_t*>(vd + 2 * lane) = v_lo;
+          *reinterpret_cast<uint32_t*>(vd + 64 + 2 * lane) = v_hi;
+        }
+      }
+    }
     for (int p = n_pre; p < n_pages; ++p) {
       const int phys = __shfl_sync(0xffffffffu, my_phys, p);
       if (lane == 0) {
         if (p >= kAttnStages) mbar_wait(&empty_bar[p % kAttnStages], ((p / kAttnStages) - 1) & 1);
         issue_page(p, phys);
+      }
+    }
+    if constexpr (FUSED) {
+      if (last_chunk) {
+        // the row's last page has landed (whatever the cache held in the new token's slot): put
+        // the fresh K/V row into its swizzled place, then let that page's consumer go
+        const int p_last = n_pages - 1;
+        const int stage = p_last % kAttnStages;
+        mbar_wait(&full_bar[stage], (p_last / kAttnStages) & 1);
+        const int r = (seq_len - 1) & (kPage - 1);
+        uint8_t* sk = ring + stage * kAttnStageBytes;
+        const int o_lo = r * 128 + (((lane >> 2) ^ (r & 7)) << 4) + (lane & 3) * 4;
+        *reinterpret_cast<uint32_t*>(sk + o_lo) = k_lo;
+        *reinterpret_cast<uint32_t*>(sk + 2048 + o_lo) = k_hi;
+        *reinterpret_cast<uint32_t*>(sk + 4096 + o_lo) = v_lo;
+        *reinterpret_cast<uint32_t*>(sk + 6144 + o_lo) = v_hi;
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&patch_bar);
       }
     }
   } else {
@@ -184,6 +380,9 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
     for (int p = warp; p < n_pages; p += kAttnConsumers) {
       const int stage = p % kAttnStages;
       mbar_wait(&full_bar[stage], (p / kAttnStages) & 1);
+      if constexpr (FUSED) {
+        if (last_chunk && p == n_pages - 1) mbar_wait(&patch_bar, 0);
+      }
       const uint32_t sk = ring_u32 + stage * kAttnStageBytes;
       const uint32_t sv = sk + 4096;
       // ---- S = Q K^T
@@ -420,15 +619,15 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
   if (tid == 0) BCG_TL(4, 5);
 }
 
-template <int G>
+template <int G, bool FUSED>
 static int launch_decode(const void* q, const void* kv_cache, const int* block_table,
                          int max_blocks, const int* seq_lens, float* scratch_o, float* scratch_ml,
                          int* counters, void* out, int B, int n_heads, int n_kv_heads,
-                         int max_splits, float scale, cudaStream_t stream) {
+                         int max_splits, float scale, const RopeFusion& rf, cudaStream_t stream) {
   constexpr int SMEM = kAttnStages * kAttnStageBytes + 1024;
   static bool configured = false;
   if (!configured) {
-    BCG_CUDA_CHECK(cudaFuncSetAttribute(decode_attn_kernel<G>,
+    BCG_CUDA_CHECK(cudaFuncSetAttribute(decode_attn_kernel<G, FUSED>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
     configured = true;
   }
@@ -438,11 +637,37 @@ static int launch_decode(const void* q, const void* kv_cache, const int* block_t
   const int rc = make_tmap_bf16_sw128(&kv_map, kv_cache, 1ll << 30, 128, 128, kPage);
   if (rc != BCG_OK) return rc;
   dim3 grid(max_splits, n_kv_heads, B);
-  BCG_CUDA_CHECK(launch_k(decode_attn_kernel<G>, grid, dim3(kAttnThreads), SMEM, stream, kv_map,
+  BCG_CUDA_CHECK(launch_k(decode_attn_kernel<G, FUSED>, grid, dim3(kAttnThreads), SMEM, stream, kv_map,
                           reinterpret_cast<const __nv_bfloat16*>(q), block_table, max_blocks, seq_lens,
                           scratch_o, scratch_ml, counters, reinterpret_cast<__nv_bfloat16*>(out),
-                          n_heads, n_kv_heads, max_splits, scale * 1.4426950408889634f));
+                          n_heads, n_kv_heads, max_splits, scale * 1.4426950408889634f, rf));
   return BCG_OK;
+}
+
+template <bool FUSED>
+static int dispatch_decode(const void* q, const void* kv_cache, const int* block_table, int max_blocks,
+                           const int* seq_lens, float* scratch_o, float* scratch_ml, int* counters,
+                           void* out, int B, int n_heads, int n_kv_heads, int max_splits, float scale,
+                           const RopeFusion& rf, cudaStream_t stream, const char* who) {
+  switch (n_heads / n_kv_heads) {
+#define BCG_DECODE_CASE(g)                                                                          \
+  case g:                                                                                           \
+    return launch_decode<g, FUSED>(q, kv_cache, block_table, max_blocks, seq_lens, scratch_o,      \
+                                   scratch_ml, counters, out, B, n_heads, n_kv_heads, max_splits,   \
+                                   scale, rf, stream);
+    BCG_DECODE_CASE(1)
+    BCG_DECODE_CASE(2)
+    BCG_DECODE_CASE(3)
+    BCG_DECODE_CASE(4)
+    BCG_DECODE_CASE(5)
+    BCG_DECODE_CASE(6)
+    BCG_DECODE_CASE(7)
+    BCG_DECODE_CASE(8)
+#undef BCG_DECODE_CASE
+    default:
+      set_last_error(who, "unsupported GQA group size (1..8)");
+      return BCG_ERR_UNSUPPORTED;
+  }
 }
 
 // `counters`: B * n_kv_heads ints, zero on entry, zero again on exit.
@@ -465,30 +690,51 @@ int decode_attn_paged(const void* q, const void* kv_cache, const int* block_tabl
     set_last_error("bcg_decode_attn_paged", "scratch_o must be 16-byte, scratch_ml and out 8-byte aligned");
     return BCG_ERR_ARG;
   }
-  const int G = n_heads / n_kv_heads;
-  int rc;
-#define BCG_DECODE_CASE(g)                                                                    \
-  case g:                                                                                     \
-    rc = launch_decode<g>(q, kv_cache, block_table, max_blocks_per_seq, seq_lens, scratch_o,  \
-                          scratch_ml, counters, out, B, n_heads, n_kv_heads, max_splits,      \
-                          scale, stream);                                                     \
-    break;
-  switch (G) {
-    BCG_DECODE_CASE(1)
-    BCG_DECODE_CASE(2)
-    BCG_DECODE_CASE(3)
-    BCG_DECODE_CASE(4)
-    BCG_DECODE_CASE(5)
-    BCG_DECODE_CASE(6)
-    BCG_DECODE_CASE(7)
-    BCG_DECODE_CASE(8)
-    default:
-      set_last_error("bcg_decode_attn_paged", "unsupported GQA group size (1..8)");
-      return BCG_ERR_UNSUPPORTED;
+  return dispatch_decode<false>(q, kv_cache, block_table, max_blocks_per_seq, seq_lens, scratch_o,
+                                scratch_ml, counters, out, B, n_heads, n_kv_heads, max_splits, scale,
+                                RopeFusion{}, stream, "bcg_decode_attn_paged");
+}
+
+// Decode attention straight from the qkv projection's split-K slabs (no qknorm_rope_kvwrite launch):
+// see the FUSED notes above decode_attn_kernel.  kv_cache is read AND written (the new token's row).
+int decode_attn_paged_qkv(const float* qkv, int n_partials, long long partial_stride, long long ld_qkv,
+                          const float* q_norm_w, const float* k_norm_w, const float* cos_sin,
+                          const int* positions, const int* slot_map, float eps, void* kv_cache,
+                          const int* block_table, int max_blocks_per_seq, const int* seq_lens, void* out,
+                          float* scratch_o, float* scratch_ml, int* counters, int B, int n_heads,
+                          int n_kv_heads, int page_size, int max_splits, float scale,
+                          cudaStream_t stream) {
+  if (!qkv || n_partials < 1 || !cos_sin || !positions || !slot_map || !kv_cache || !block_table ||
+      !seq_lens || !out || !scratch_o || !scratch_ml || !counters || B <= 0 || n_heads <= 0 ||
+      n_kv_heads <= 0 || max_splits <= 0 || (n_heads % n_kv_heads) || (ld_qkv % 4) ||
+      (partial_stride % 4) || (reinterpret_cast<uintptr_t>(qkv) & 15)) {
+    set_last_error("bcg_decode_attn_paged_qkv", "bad argument");
+    return BCG_ERR_ARG;
   }
-#undef BCG_DECODE_CASE
-  if (rc != BCG_OK) return rc;
-  return BCG_OK;
+  if (page_size != kPage) {
+    set_last_error("bcg_decode_attn_paged_qkv", "page_size must be 16");
+    return BCG_ERR_UNSUPPORTED;
+  }
+  if ((reinterpret_cast<uintptr_t>(scratch_o) & 15) || (reinterpret_cast<uintptr_t>(scratch_ml) & 7) ||
+      (reinterpret_cast<uintptr_t>(out) & 7)) {
+    set_last_error("bcg_decode_attn_paged_qkv", "scratch_o must be 16-byte, scratch_ml and out 8-byte aligned");
+    return BCG_ERR_ARG;
+  }
+  RopeFusion rf;
+  rf.qkv = qkv;
+  rf.n_partials = n_partials;
+  rf.partial_stride = partial_stride;
+  rf.ld_qkv = ld_qkv;
+  rf.q_norm_w = q_norm_w;
+  rf.k_norm_w = k_norm_w;
+  rf.cos_sin = cos_sin;
+  rf.positions = positions;
+  rf.slot_map = slot_map;
+  rf.kv_cache = reinterpret_cast<__nv_bfloat16*>(kv_cache);
+  rf.eps = eps;
+  return dispatch_decode<true>(nullptr, kv_cache, block_table, max_blocks_per_seq, seq_lens, scratch_o,
+                               scratch_ml, counters, out, B, n_heads, n_kv_heads, max_splits, scale, rf,
+                               stream, "bcg_decode_attn_paged_qkv");
 }
 
 // ---------------------------------------------------------------------------------------

@@ -108,6 +108,20 @@ int bcg_decode_attn_paged(const void* q, const void* kv_cache, const int* block_
                            scale, S(stream));
 }
 
+int bcg_decode_attn_paged_qkv(const float* qkv, int n_partials, long long partial_stride,
+                              long long ld_qkv, const float* q_norm_w, const float* k_norm_w,
+                              const float* cos_sin, const int* positions, const int* slot_map,
+                              float eps, void* kv_cache, const int* block_table,
+                              int max_blocks_per_seq, const int* seq_lens, void* out, float* scratch_o,
+                              float* scratch_ml, int* chunk_counters, int B, int n_heads,
+                              int n_kv_heads, int page_size, int max_splits, float scale,
+                              void* stream) {
+  return decode_attn_paged_qkv(qkv, n_partials, partial_stride, ld_qkv, q_norm_w, k_norm_w, cos_sin,
+                               positions, slot_map, eps, kv_cache, block_table, max_blocks_per_seq,
+                               seq_lens, out, scratch_o, scratch_ml, chunk_counters, B, n_heads,
+                               n_kv_heads, page_size, max_splits, scale, S(stream));
+}
+
 int bcg_decode_attn_paged_static(const void* q, const void* kv_cache, const int* block_table,
                                  int max_blocks_per_seq, const int* seq_lens, void* out, int B,
                                  int n_heads, int n_kv_heads, int page_size, int max_splits,

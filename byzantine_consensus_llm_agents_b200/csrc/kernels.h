@@ -41,6 +41,13 @@ int decode_attn_paged(const void* q, const void* kv_cache, const int* block_tabl
                       int max_blocks_per_seq, const int* seq_lens, void* out, float* scratch_o,
                       float* scratch_ml, int* counters, int B, int n_heads, int n_kv_heads,
                       int page_size, int max_splits, float scale, cudaStream_t stream);
+int decode_attn_paged_qkv(const float* qkv, int n_partials, long long partial_stride, long long ld_qkv,
+                          const float* q_norm_w, const float* k_norm_w, const float* cos_sin,
+                          const int* positions, const int* slot_map, float eps, void* kv_cache,
+                          const int* block_table, int max_blocks_per_seq, const int* seq_lens, void* out,
+                          float* scratch_o, float* scratch_ml, int* counters, int B, int n_heads,
+                          int n_kv_heads, int page_size, int max_splits, float scale,
+                          cudaStream_t stream);
 int decode_attn_paged_static(const void* q, const void* kv_cache, const int* block_table,
                              int max_blocks_per_seq, const int* seq_lens, void* out, int B,
                              int n_heads, int n_kv_heads, int page_size, int max_splits, float scale,

@@ -137,6 +137,8 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
     ~FlagScope() { launch_flags() = saved; }
   } scope(gf);
   float* P = ws->partials;
+  // qk-norm / RoPE / KV-write folded into decode attention (bcg_decode_attn_paged_qkv)
+  const bool fuse_rope = (flags & BCG_STEP_FUSED_ROPE) && !skip_rope;
   // Norm fusion (single GPU, opt-in with BCG_STEP_FUSED_NORM): the o / down projections finish the
   // residual add and leave bf16(residual * w) plus per-tile sums of squares; the projection that
   // follows applies 1/RMS in its epilogue.  No add_rmsnorm kernel runs after layer 0's embedding
@@ -190,6 +192,16 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
       BCG_TRY(gemm_bf16_tn_fused(ws->xn, m->w_qkv[l], P, B, qkv_dim, d, d, d, qkv_dim, BCG_EPI_F32, s_qkv,
                                  gf, ((nf || dn) && l > 0) ? &f : nullptr, st));
     }
+    if (fuse_rope) {
+      if (!skip_attn)
+      BCG_TRY(decode_attn_paged_qkv(P, s_qkv, static_cast<long long>(B) * qkv_dim, qkv_dim,
+                                    m->q_norm ? static_cast<const float*>(m->q_norm[l]) : nullptr,
+                                    m->k_norm ? static_cast<const float*>(m->k_norm[l]) : nullptr,
+                                    static_cast<const float*>(m->cos_sin), positions, slot_map, m->rms_eps,
+                                    m->kv_cache[l], block_table, max_blocks, seq_lens, ws->attn,
+                                    ws->attn_scratch_o, ws->attn_scratch_ml, ws->attn_counters, B, hq, hkv,
+                                    m->page_size, ws->max_splits, scale, st));
+    } else {
     if (!skip_rope)
     BCG_TRY(qknorm_rope_kvwrite(P, 1, s_qkv, static_cast<long long>(B) * qkv_dim, qkv_dim,
                                 m->q_norm ? m->q_norm[l] : nullptr,
@@ -199,6 +211,7 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
     BCG_TRY(decode_attn_paged(ws->q, m->kv_cache[l], block_table, max_blocks, seq_lens, ws->attn,
                               ws->attn_scratch_o, ws->attn_scratch_ml, ws->attn_counters, B, hq, hkv,
                               m->page_size, ws->max_splits, scale, st));
+    }
     if (fused) {
       // row-parallel projection straight into the symmetric buffer; the norm kernel sums every
       // rank's slabs from peer memory

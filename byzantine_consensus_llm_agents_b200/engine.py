@@ -147,6 +147,7 @@ class Engine:
                  gpu_memory_utilization: float = 0.9, base_seed: int = 0, device: str = "cuda:0",
                  enable_prefix_cache: bool = True, use_cuda_graph: bool = True, pdl: bool = False,
                  fused_norm: bool = False, deferred_norm: Optional[bool] = None,
+                 fused_rope: bool = False,
                  tp_rank: int = 0, tp_size: int = 1, tp_fused_allreduce: bool = True, tp_group=None):
         """`cfg` is the FULL architecture; with tp_size > 1 `weights` must be this rank's shard
         (Weights.shard / random_init_sharded) and bcg_tp_init must have been called (collective)."""
@@ -175,7 +176,8 @@ class Engine:
         if deferred_norm is None:
             deferred_norm = tp_size == 1 and not fused_norm
         self.flags = ((L.GEMM_PDL if pdl else 0) | (L.STEP_FUSED_NORM if fused_norm else 0)
-                      | (L.STEP_DEFERRED_NORM if deferred_norm else 0))
+                      | (L.STEP_DEFERRED_NORM if deferred_norm else 0)
+                      | (L.STEP_FUSED_ROPE if fused_rope else 0))
         self.max_blocks = (self.max_model_len + PAGE - 1) // PAGE
         self.max_steps = self.max_model_len
 

@@ -15,6 +15,7 @@ LIB_PATH = PKG / "_lib" / "libbcg_b200.so"
 EPI_BF16, EPI_F32, EPI_SWIGLU = 0, 1, 2
 GEMM_PDL = 1
 STEP_FUSED_NORM = 0x20000   # bcg_model_decode: fold add+RMSNorm into the GEMMs (opt-in, slower)
+STEP_FUSED_ROPE = 0x80000     # bcg_model_decode: qk-norm/RoPE/KV-write folded into decode attention
 STEP_DEFERRED_NORM = 0x40000  # bcg_model_decode: norm statistics kernel + 1/RMS in the next GEMM's epilogue
 
 c_int_p = C.POINTER(C.c_int)
@@ -94,6 +95,9 @@ _SIGS = {
     "bcg_swiglu_reduce": (C.c_int, [vp, C.c_int, C.c_longlong, vp, C.c_int, C.c_int, vp]),
     "bcg_decode_attn_paged": (C.c_int, [vp, vp, vp, C.c_int, vp, vp, vp, vp, vp, C.c_int, C.c_int,
                                         C.c_int, C.c_int, C.c_int, C.c_float, vp]),
+    "bcg_decode_attn_paged_qkv": (C.c_int, [vp, C.c_int, C.c_longlong, C.c_longlong, vp, vp, vp, vp, vp, C.c_float,
+                                            vp, vp, C.c_int, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int,
+                                            C.c_int, C.c_int, C.c_float, vp]),
     "bcg_decode_attn_paged_static": (C.c_int, [vp, vp, vp, C.c_int, vp, vp, C.c_int, C.c_int, C.c_int,
                                                C.c_int, C.c_int, C.c_float, vp]),
     "bcg_prefill_attn_paged": (C.c_int, [vp, vp, vp, C.c_int, vp, C.c_int, vp, C.c_int, C.c_int,

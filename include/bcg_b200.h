@@ -136,6 +136,23 @@ int bcg_decode_attn_paged(const void* q, const void* kv_cache, const int* block_
                           float* scratch_ml, int* chunk_counters, int B, int n_heads, int n_kv_heads,
                           int page_size, int max_splits, float scale, void* stream);
 
+/* bcg_qknorm_rope_kvwrite + bcg_decode_attn_paged in ONE launch (decode only): takes the qkv
+ * projection's fp32 split-K slabs [n_partials][B, ld_qkv] (q heads | k heads | v heads) and the
+ * RoPE / norm / slot arguments of bcg_qknorm_rope_kvwrite.  Every chunk CTA rebuilds its queries
+ * itself; the CTA of a row's last chunk also builds the new token's K/V row, writes it to
+ * kv_cache (slot_map[b], negative = skip) and patches it into the page it streamed in.  Stands in
+ * for the same vLLM ops as the two entry points it replaces (`_C.rotary_embedding`,
+ * `reshape_and_cache_flash`, FlashInfer paged decode).  Other arguments as
+ * for bcg_decode_attn_paged. */
+int bcg_decode_attn_paged_qkv(const float* qkv, int n_partials, long long partial_stride,
+                              long long ld_qkv, const float* q_norm_w, const float* k_norm_w,
+                              const float* cos_sin, const int* positions, const int* slot_map,
+                              float eps, void* kv_cache, const int* block_table,
+                              int max_blocks_per_seq, const int* seq_lens, void* out, float* scratch_o,
+                              float* scratch_ml, int* chunk_counters, int B, int n_heads,
+                              int n_kv_heads, int page_size, int max_splits, float scale,
+                              void* stream);
+
 /* Same computation as bcg_decode_attn_paged, for callers that cannot allocate device memory.
  * No counterpart in the reference (the reference never manages device memory itself); it exists
  * for hosts of this library that have no memory left to give, or no safe moment to ask for it:
@@ -297,6 +314,7 @@ int bcg_model_prefill(const bcg_model* m, const bcg_workspace* ws, const int* id
  *                             (bcg_gemm_bf16_tn_fused producer half; measured slower) */
 #define BCG_STEP_FUSED_NORM 0x20000
 #define BCG_STEP_DEFERRED_NORM 0x40000
+#define BCG_STEP_FUSED_ROPE 0x80000 /* bcg_decode_attn_paged_qkv instead of rope kernel + attention */
 int bcg_model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids,
                      const int* positions, const int* slot_map, const int* seq_lens,
                      const int* block_table, int max_blocks_per_seq, int B, int flags,

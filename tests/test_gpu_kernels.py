@@ -542,6 +542,72 @@ def test_decode_attn_paged(H, HKV, lens):
         assert err <= 2e-2, f"row {b} len {lens[b]} err {err}"  # bf16 output of O(1) values
 
 
+@pytest.mark.parametrize("H,HKV,lens,parts,qknorm", [
+    (40, 8, [1600, 257, 1, 16, 17, 512, 300], 5, True),      # 14B shape: chunk / page boundaries, 1-token row
+    (8, 8, [33, 700], 1, True),                               # G = 1
+    (48, 8, [1025, 64], 3, False),                            # no QK-norm (Mistral), G = 6
+    (64, 8, [2049, 900, 4100], 2, True),                      # G = 8, rows with more than 8 chunks
+    (4, 2, [5, 256], 11, True)])
+def test_decode_attn_from_qkv_slabs_equals_rope_kernel_plus_attention(H, HKV, lens, parts, qknorm):
+    """bcg_decode_attn_paged_qkv == bcg_qknorm_rope_kvwrite followed by bcg_decode_attn_paged: the KV
+    cache ends up bit-identical (the new token's K/V use the rope kernel's arithmetic), the outputs
+    agree to bf16 rounding of the queries (their RMS is summed in a different lane order)."""
+    lib = _lib()
+    B, G = len(lens), H // HKV
+    qkv_dim = (H + 2 * HKV) * 128
+    cache0, bt, _, _ = _build_paged(lens, HKV, seed=60)
+    # garbage where the new token goes: neither path may read it
+    cos_sin = _make_cos_sin(max_pos=8192)
+    pos = torch.tensor([n - 1 for n in lens], device=DEV, dtype=torch.int32)
+    slots = torch.tensor([int(bt[b, (n - 1) // 16]) * 16 + (n - 1) % 16 for b, n in enumerate(lens)],
+                         device=DEV, dtype=torch.int32)
+    for b, n in enumerate(lens):
+        cache0[int(bt[b, (n - 1) // 16]), :, :, (n - 1) % 16] = float("nan")
+    slots_skip = slots.clone()
+    if B > 2:
+        slots_skip[2] = -1   # a row that must not write the cache (its attention still sees the new token)
+    seq = torch.tensor(lens, device=DEV, dtype=torch.int32)
+    P = torch.randn(parts, B, qkv_dim, device=DEV) * 0.7
+    qw = (torch.rand(128, device=DEV) + 0.5) if qknorm else None
+    kw = (torch.rand(128, device=DEV) + 0.5) if qknorm else None
+    max_splits = (max(lens) + 255) // 256
+    so = torch.empty(B * H * max_splits * 128, device=DEV)
+    sml = torch.empty(B * H * max_splits * 2, device=DEV)
+    cnt = torch.zeros(B * HKV, device=DEV, dtype=torch.int32)
+    scale = 1.0 / math.sqrt(128)
+    # reference path: two launches
+    cache_a = cache0.clone()
+    q = torch.empty(B, H * 128, device=DEV, dtype=torch.bfloat16)
+    out_a = torch.empty(B, H * 128, device=DEV, dtype=torch.bfloat16)
+    L.check(lib.bcg_qknorm_rope_kvwrite(P.data_ptr(), 1, parts, B * qkv_dim, qkv_dim, L.ptr(qw), L.ptr(kw),
+                                        cos_sin.data_ptr(), pos.data_ptr(), slots.data_ptr(), q.data_ptr(),
+                                        cache_a.data_ptr(), B, H, HKV, 16, 1e-6, L.stream_ptr()))
+    L.check(lib.bcg_decode_attn_paged(q.data_ptr(), cache_a.data_ptr(), bt.data_ptr(), bt.shape[1], seq.data_ptr(),
+                                      out_a.data_ptr(), so.data_ptr(), sml.data_ptr(), cnt.data_ptr(), B, H, HKV,
+                                      16, max_splits, scale, L.stream_ptr()))
+    torch.cuda.synchronize()
+    for trial_slots in (slots, slots_skip):
+        cache_b = cache0.clone()
+        out_b = torch.full((B, H * 128), float("nan"), device=DEV, dtype=torch.bfloat16)
+        for _ in range(2):  # second call: the row is already in the cache, the result must not change
+            L.check(lib.bcg_decode_attn_paged_qkv(P.data_ptr(), parts, B * qkv_dim, qkv_dim, L.ptr(qw), L.ptr(kw),
+                                                  cos_sin.data_ptr(), pos.data_ptr(), trial_slots.data_ptr(), 1e-6,
+                                                  cache_b.data_ptr(), bt.data_ptr(), bt.shape[1], seq.data_ptr(),
+                                                  out_b.data_ptr(), so.data_ptr(), sml.data_ptr(), cnt.data_ptr(),
+                                                  B, H, HKV, 16, max_splits, scale, L.stream_ptr()))
+            torch.cuda.synchronize()
+            assert int(cnt.abs().sum()) == 0
+            assert torch.isfinite(out_b.float()).all()
+            assert (out_b.float() - out_a.float()).abs().max().item() <= 1.5e-2
+        written = [b for b in range(B) if int(trial_slots[b]) >= 0]
+        for b in range(B):
+            pg, off = int(bt[b, (lens[b] - 1) // 16]), (lens[b] - 1) % 16
+            if b in written:
+                assert torch.equal(cache_b[pg, :, :, off].view(torch.int16), cache_a[pg, :, :, off].view(torch.int16))
+            else:
+                assert torch.isnan(cache_b[pg, :, :, off].float()).all()   # untouched
+
+
 def test_decode_attn_batch_invariance():
     lib = _lib()
     H, HKV = 40, 8

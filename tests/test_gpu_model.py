@@ -73,8 +73,9 @@ def test_logits_match_fp32_cpu_forward(cfg, tol):
     print(f"{cfg.name}: worst |dlogit| = {worst:.4f}")
 
 
-@pytest.mark.parametrize("mode", [{"fused_norm": True}, {"deferred_norm": False}, {"deferred_norm": True}],
-                         ids=["fused", "complete", "deferred"])
+@pytest.mark.parametrize("mode", [{"fused_norm": True}, {"deferred_norm": False}, {"deferred_norm": True},
+                                  {"fused_rope": True}, {"fused_rope": False}],
+                         ids=["fused", "complete", "deferred", "rope-in-attention", "rope-kernel"])
 @pytest.mark.parametrize("cfg", [TINY_QWEN, TINY_MISTRAL], ids=lambda c: c.name)
 def test_every_norm_decode_path_matches_fp32_forward(cfg, mode):
     """The three ways decode can run the residual add + RMSNorm between projections: statistics

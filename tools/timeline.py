@@ -108,11 +108,12 @@ def main():
         gem[p] = t.reshape(n_gemm, per)
     have_norm = (2, 0) in ev
     norm = {p: instances_by_gap(ev[(2, p)], 8000) for p in (0, 1, 3, 4, 5, 6, 7) if (2, p) in ev} if have_norm else {0: []}
-    rope = {p: instances_by_gap(ev[(3, p)], 30000) for p in (0, 1)}
+    have_rope = (3, 0) in ev
+    rope = {p: instances_by_gap(ev[(3, p)], 30000) for p in (0, 1)} if have_rope else {}
     att = {p: instances_by_gap(ev[(4, p)], 30000) for p in (0, 1, 2)}
     att_exit = instances_by_gap(np.concatenate([ev[(4, 3)], ev.get((4, 5), np.zeros(0, np.int64))]), 30000)
     print(f"{a.model} rows={nb} ctx={a.ctx}: gemm CTAs/instance {gem[0].shape[1]}, norm instances "
-          f"{len(norm[0])}, rope {len(rope[0])}, attention {len(att[0])}")
+          f"{len(norm[0])}, rope {len(rope[0]) if have_rope else 0}, attention {len(att[0])}")
     step_ns = gem[3][-1].max() - gem[0][0].min()
     print(f"step (first GEMM entry -> lm_head exit): {step_ns / 1e6:.3f} ms")
 
@@ -135,8 +136,9 @@ def main():
             e[f"{nm} GEMM last load issued first/last"] = (gem[2][gi].min(), gem[2][gi].max())
             e[f"{nm} GEMM epilogue done first/last"] = (gem[3][gi].min(), gem[3][gi].max())
             if nm == "qkv":
-                e["rope entry"] = rope[0][l].min()
-                e["rope past wait"] = rope[1][l].min()
+                if have_rope:
+                    e["rope entry"] = rope[0][l].min()
+                    e["rope past wait"] = rope[1][l].min()
                 e["attn entry first/last"] = (att[0][l].min(), att[0][l].max())
                 e["attn past wait first/last"] = (att[1][l].min(), att[1][l].max())
                 e["attn loop done first/last"] = (att[2][l].min(), att[2][l].max())
