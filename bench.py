@@ -167,15 +167,18 @@ def kernel_roofline(engine, B: int, hbm_peak: float, peak_kind: str):
     if splits > 1:
         out = engine.buf["partials"][:splits * B * N].view(splits, B, N)
     layers = len(w.w_gate_up)
+    # launched the way the decode step launches it: programmatic dependent launch when the engine
+    # uses it (a launch's weight prefetch then overlaps its predecessor's drain, as in the step)
+    gflags = engine.flags & L.GEMM_PDL
     for l in range(min(3, layers)):
-        L.gemm(x, w.w_gate_up[l], out, epi, splits=splits)
+        L.gemm(x, w.w_gate_up[l], out, epi, splits=splits, flags=gflags)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     reps = 3
     e0.record()
     for _ in range(reps):
         for l in range(layers):          # 40 different weight matrices: 14 GB >> 126 MB L2
-            L.gemm(x, w.w_gate_up[l], out, epi, splits=splits)
+            L.gemm(x, w.w_gate_up[l], out, epi, splits=splits, flags=gflags)
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / (reps * layers)
@@ -189,7 +192,8 @@ def kernel_roofline(engine, B: int, hbm_peak: float, peak_kind: str):
         except Exception:
             traffic = None
     return {"kernel": f"gemm_tcgen05_kernel<BN={16 if B <= 16 else 32 if B <= 32 else 64 if B <= 64 else 128}> "
-                      f"(decode gate_up: M={B}, N={N}, K={K}, splits={splits})",
+                      f"(decode gate_up: M={B}, N={N}, K={K}, splits={splits}"
+                      f"{', back-to-back launches with programmatic dependent launch' if gflags else ''})",
             "bound": "hbm", "achieved": round(achieved, 1), "peak": hbm_peak, "peak_kind": peak_kind,
             "unit": "GB/s", "frac": round(achieved / hbm_peak, 4), "traffic": traffic,
             "us_per_launch": round(ms * 1e3, 2), "algorithmic_bytes_per_launch": alg_bytes}
