@@ -123,6 +123,11 @@ __device__ __forceinline__ float4 residual_plus_delta(const float* __restrict__ 
     return r;
   }
   const float* dp = reinterpret_cast<const float*>(delta) + off;
+  if (n_partials == 1) {  // prefill: one fp32 slab, no reason to issue clamped duplicates
+    const float4 p0 = *reinterpret_cast<const float4*>(dp);
+    r.x += p0.x; r.y += p0.y; r.z += p0.z; r.w += p0.w;
+    return r;
+  }
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
   for (int s0 = 0; s0 < n_partials; s0 += BATCH) {
     float4 p[BATCH];
@@ -378,6 +383,10 @@ qknorm_rope_kvwrite_kernel(const void* __restrict__ qkv, int qkv_is_f32, int n_p
       // slabs are requested eight at a time, unconditionally (indices past the end re-read the last
       // slab and are ignored), and added in index order
       float2 a = make_float2(0.f, 0.f), b = make_float2(0.f, 0.f);
+      if (n_partials == 1) {  // prefill: a single slab
+        a = *reinterpret_cast<const float2*>(p + 2 * lane);
+        b = *reinterpret_cast<const float2*>(p + 64 + 2 * lane);
+      } else
       for (int s0 = 0; s0 < n_partials; s0 += 8) {
         float2 pa[8], pb[8];
 #pragma unroll
