@@ -221,13 +221,16 @@ def test_waves_and_prefill_groups_do_not_change_results():
     assert all(r.prompt_tokens == n for r, n in zip(together, lens))
 
 
-def test_qwen3_14b_width_reduced_depth_logits():
+@pytest.mark.parametrize("preset,n_layers", [("qwen3-14b", 4), ("qwen3-8b", 2), ("qwen3-32b", 2)])
+def test_qwen3_14b_width_reduced_depth_logits(preset, n_layers):
     """The headline architecture's width (d 5120, 40/8 heads, d_ff 17408, 151,936 vocabulary) at
-    4 layers: prefill + decode logits against the fp32 CPU forward (full depth needs 59 GB of fp32
-    on the host and minutes of CPU time; depth does not change which kernels and shapes run)."""
+    4 layers — and the 8B (d 4096, 32/8 heads) and 32B (d 5120, 64/8 heads, d_ff 25600) widths of the
+    other BASELINE configs at 2 — prefill + decode logits against the fp32 CPU forward (full depth
+    needs 59 GB of fp32 on the host and minutes of CPU time; depth does not change which kernels and
+    shapes run)."""
     from byzantine_consensus_llm_agents_b200.model import PRESETS
-    full = PRESETS["qwen3-14b"]
-    cfg = ModelConfig(**{**full.__dict__, "n_layers": 4, "name": "qwen3-14b-L4"})
+    full = PRESETS[preset]
+    cfg = ModelConfig(**{**full.__dict__, "n_layers": n_layers, "name": f"{preset}-L{n_layers}"})
     hf = build_hf_model(cfg, seed=0)
     w = Weights.from_hf_state_dict(cfg, hf.state_dict(), torch.device("cuda:0"))
     tk = get_tokenizer(cfg.family, cfg.vocab)
@@ -250,7 +253,7 @@ def test_qwen3_14b_width_reduced_depth_logits():
         d = (got[:, b] - ref).abs()
         rms = d.pow(2).mean().sqrt().item()
         std = ref.std().item()
-        print(f"14B-width L4 row {b}: max |dlogit| {d.max().item():.4f}  rms {rms:.5f} logit std {std:.3f}")
+        print(f"{cfg.name} row {b}: max |dlogit| {d.max().item():.4f}  rms {rms:.5f} logit std {std:.3f}")
         worst = max(worst, d.max().item() / std)
         assert rms <= 1.5e-2 * std, (rms, std)
         # greedy decisions survive: wherever the oracle's top-2 margin exceeds twice the worst
