@@ -145,7 +145,7 @@ class Engine:
     def __init__(self, cfg: ModelConfig, weights: Weights, tokenizer, *, max_model_len: int = 8192,
                  max_rows: int = 64, prefill_tokens: int = 16384, kv_pages: Optional[int] = None,
                  gpu_memory_utilization: float = 0.9, base_seed: int = 0, device: str = "cuda:0",
-                 enable_prefix_cache: bool = True, use_cuda_graph: bool = True, pdl: bool = False,
+                 enable_prefix_cache: bool = True, use_cuda_graph: bool = True, pdl: bool = True,
                  fused_norm: bool = False, deferred_norm: Optional[bool] = None,
                  fused_rope: bool = False,
                  tp_rank: int = 0, tp_size: int = 1, tp_fused_allreduce: bool = True, tp_group=None):
