@@ -146,6 +146,27 @@ def test_cuda_graph_equals_eager_and_batch_invariant():
             assert st >= 0
 
 
+def test_launch_mode_does_not_change_results():
+    """Programmatic dependent launch only changes WHEN kernels start (prefetch before the dependency
+    wait), never what they compute: logits and sampled tokens are bit-identical with it on or off,
+    through the CUDA graph and eagerly."""
+    outs = []
+    for pdl in (True, False):
+        hf, eng, tk = _setup(TINY_QWEN, pdl=pdl, base_seed=5)
+        rng = np.random.default_rng(9)
+        prompts = _prompts(tk, rng, [300, 17, 64])
+        schema = {"type": "object", "properties": {"value": {"type": "integer", "minimum": 0, "maximum": 50}},
+                  "required": ["value"], "additionalProperties": False}
+        sampled = eng.generate([Request("", schema, 0.7, 30, prompt_ids=p) for p in prompts])
+        eng.calls = 0
+        eng.debug_logits = []
+        forced = [rng.integers(*tk.regular_range, size=6).tolist() for _ in prompts]
+        eng.generate([Request("", None, 0.0, 6, forced=f, prompt_ids=p) for p, f in zip(prompts, forced)])
+        outs.append(([r.token_ids for r in sampled], torch.stack(eng.debug_logits).cpu()))
+    assert outs[0][0] == outs[1][0]
+    assert torch.equal(outs[0][1], outs[1][1])
+
+
 def test_seeded_sampling_is_reproducible_and_temperature_matters():
     hf, eng, tk = _setup(TINY_QWEN, base_seed=11)
     rng = np.random.default_rng(3)
