@@ -167,6 +167,31 @@ def test_launch_mode_does_not_change_results():
     assert torch.equal(outs[0][1], outs[1][1])
 
 
+def test_launch_mode_does_not_change_results_at_full_width():
+    """Same, at the 14B width with 10 rows and ~700-token contexts — the shapes at which the kernels
+    really overlap (weight / KV prefetch of one kernel running under the tail of the one before):
+    any read that raced with its producer would show up as a difference."""
+    from byzantine_consensus_llm_agents_b200.model import PRESETS
+    full = PRESETS["qwen3-14b"]
+    cfg = ModelConfig(**{**full.__dict__, "n_layers": 3, "name": "qwen3-14b-L3"})
+    w = Weights.random_init(cfg, torch.device("cuda:0"))
+    tk = get_tokenizer(cfg.family, cfg.vocab)
+    rng = np.random.default_rng(21)
+    lo, hi = tk.regular_range
+    prompts = [rng.integers(lo, hi, size=n).tolist() for n in (700, 650, 512, 300, 257, 256, 129, 64, 17, 5)]
+    outs = []
+    for kw in ({"pdl": True}, {"pdl": False}, {"pdl": True, "fused_rope": True}):
+        eng = Engine(cfg, w, tk, max_model_len=1024, max_rows=16, prefill_tokens=4096, kv_pages=700,
+                     base_seed=3, **kw)
+        res = eng.generate([Request("", None, 0.9, 48, prompt_ids=p) for p in prompts])
+        outs.append([r.token_ids for r in res])
+        eng.close()
+    assert outs[0] == outs[1]
+    # the fused rope path builds q with a different summation order: its tokens may differ, but it
+    # must be deterministic and complete
+    assert all(len(t) == 48 for t in outs[2])
+
+
 def test_seeded_sampling_is_reproducible_and_temperature_matters():
     hf, eng, tk = _setup(TINY_QWEN, base_seed=11)
     rng = np.random.default_rng(3)
