@@ -141,9 +141,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       // Under programmatic dependent launch this CTA may start while the previous kernel is still
       // running.  Weights never depend on it, activations do: so the weight halves of the first
       // kPreWaitStages ring slots are requested right away and only then does the producer wait
-      // for the previous kernel and add the activation halves.  (Measured on the 14B decode step:
-      // 1 slot 6.24 ms, 4 slots 6.15, 6 slots 5.97, all 10 slots 6.03 — deeper prefetch starts
-      // to take bandwidth from the predecessor; pulling further tiles into L2 with
+      // for the previous kernel and add the activation halves.  (Measured on the 14B decode step
+      // with the two-CTA configuration: 1 slot 5.61 ms, 2: 5.57, 3: 5.47, 4: 5.45, all 6: 5.40.
+      // With the earlier one-CTA 10-stage ring 6 of 10 was best; pulling further tiles into L2 with
       // cp.async.bulk.prefetch made the step monotonically slower, 6.16 -> 6.93 ms at 64 tiles.)
       int n_pre = 0;
       if (args.pdl_wait_b) {
