@@ -100,19 +100,30 @@ def main():
     nl = cfg.n_layers
     # GEMM: every instance has the same CTA count -> chunk the sorted stamps; others: split on gaps
     n_gemm = 4 * nl + 1
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    slots = 2 * sms if nb <= 32 else sms          # two CTAs per SM for decode batches of <= 32 rows
+    d = cfg.d_model
+
+    def ctas(n, k, fixed_splits=None):
+        sp = fixed_splits or L.splits_for(nb, n, k)
+        return min(slots, ((n + 127) // 128) * sp)
+
+    s_gu = L.splits_for(nb, 2 * cfg.d_ff, d)
+    per_layer = [ctas(cfg.qkv_dim, d), ctas(d, cfg.n_heads * 128), ctas(2 * cfg.d_ff, d), ctas(d, cfg.d_ff)]
+    counts = per_layer * nl + [ctas(cfg.vocab, d, 1)]
+    bounds = np.concatenate([[0], np.cumsum(counts)])
     gem = {}
     for p in (0, 1, 2, 3):
         t = np.sort(ev[(1, p)])
-        per = len(t) // n_gemm
-        assert per * n_gemm == len(t), (p, len(t), n_gemm)
-        gem[p] = t.reshape(n_gemm, per)
+        assert len(t) == bounds[-1], (p, len(t), int(bounds[-1]))
+        gem[p] = [t[bounds[i]:bounds[i + 1]] for i in range(n_gemm)]
     have_norm = (2, 0) in ev
     norm = {p: instances_by_gap(ev[(2, p)], 8000) for p in (0, 1, 3, 4, 5, 6, 7) if (2, p) in ev} if have_norm else {0: []}
     have_rope = (3, 0) in ev
     rope = {p: instances_by_gap(ev[(3, p)], 30000) for p in (0, 1)} if have_rope else {}
     att = {p: instances_by_gap(ev[(4, p)], 30000) for p in (0, 1, 2)}
     att_exit = instances_by_gap(np.concatenate([ev[(4, 3)], ev.get((4, 5), np.zeros(0, np.int64))]), 30000)
-    print(f"{a.model} rows={nb} ctx={a.ctx}: gemm CTAs/instance {gem[0].shape[1]}, norm instances "
+    print(f"{a.model} rows={nb} ctx={a.ctx}: gemm CTAs/instance {per_layer}, norm instances "
           f"{len(norm[0])}, rope {len(rope[0]) if have_rope else 0}, attention {len(att[0])}")
     step_ns = gem[3][-1].max() - gem[0][0].min()
     print(f"step (first GEMM entry -> lm_head exit): {step_ns / 1e6:.3f} ms")
@@ -124,7 +135,6 @@ def main():
         t0 = gem[1][4 * l].min()  # qkv GEMM: first CTA past its wait
         e = {}
         if have_norm:
-            e["normA entry (prev layer's down->norm)"] = norm[0][2 * l - 1].min()
             e["normA past wait"] = norm[1][2 * l - 1].min()
             e["normA exit (last CTA)"] = norm[3][2 * l - 1].max()
         else:
@@ -144,7 +154,6 @@ def main():
                 e["attn loop done first/last"] = (att[2][l].min(), att[2][l].max())
                 e["attn exit first/last"] = (att_exit[l].min(), att_exit[l].max())
             if nm == "o" and have_norm:
-                e["normB entry"] = norm[0][2 * l].min()
                 e["normB past wait first/last"] = (norm[1][2 * l].min(), norm[1][2 * l].max())
                 if 4 in norm:  # the complete (cluster) norm stamps its phases; the statistics kernel does not
                     e["normB loads+block sum done first/last"] = (norm[4][2 * l].min(), norm[4][2 * l].max())
