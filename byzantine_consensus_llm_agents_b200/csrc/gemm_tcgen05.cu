@@ -29,12 +29,13 @@ constexpr int kUmmaK = 16;
 constexpr int kGemmThreads = 192;
 
 constexpr int kSumsqStride = 128;  // rows per tile entry of the sum-of-squares tables (M <= 128)
-// Decode batches of up to 32 rows run TWO CTAs per SM with a short ring each (6 x 18 KB at 16 rows,
-// 5 x 20 KB at 32) instead of one CTA with a 10-stage ring: 296 work slots make every decode GEMM
+// Decode batches run TWO CTAs per SM with a short ring each (6 x 18 KB at 16 rows, 5 x 20 KB at 32,
+// 4 x 24 KB at 64, 3 x 32 KB at 128) instead of one CTA with a 10-stage ring: 296 work slots make every decode GEMM
 // of the 14B model a single, perfectly balanced wave (272-280 items), more bytes are in flight per
 // SM (216 KB), and the next kernel's CTAs move into a slot as soon as ONE of the two CTAs on an SM
 // has finished.  Step time 5.76 -> 5.33 ms (81 -> 88 % of the measured HBM peak).
-constexpr int kTwoCtaMaxBN = 32;
+constexpr int kTwoCtaRingBytes = 112 * 1024;  // a CTA with a ring this small shares its SM with a second one
+constexpr bool two_cta(int bn, int stages) { return stages * (128 * 64 * 2 + bn * 64 * 2) <= kTwoCtaRingBytes; }
 constexpr int kPreWaitStages = 6;  // weight slots requested before griddepcontrol.wait
 
 struct GemmArgs {
@@ -71,7 +72,7 @@ __device__ __forceinline__ float silu_mul(float g, float u) {
 }
 
 template <int BN, int STAGES>
-__global__ void __launch_bounds__(kGemmThreads, BN <= kTwoCtaMaxBN ? 2 : 1)
+__global__ void __launch_bounds__(kGemmThreads, two_cta(BN, STAGES) ? 2 : 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                     const __grid_constant__ CUtensorMap tmap_b, const GemmArgs args) {
   constexpr int A_BYTES = kBlockA * kBlockK * 2;
@@ -498,7 +499,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmA
   }
   const int total = a.tiles_a * a.tiles_b * a.splits;
   cudaLaunchConfig_t cfg = {};
-  const int slots = BN <= kTwoCtaMaxBN ? 2 * num_sms() : num_sms();
+  const int slots = two_cta(BN, STAGES) ? 2 * num_sms() : num_sms();
   cfg.gridDim = dim3(static_cast<unsigned>(total < slots ? total : slots));
   cfg.blockDim = dim3(kGemmThreads);
   cfg.dynamicSmemBytes = SMEM;
@@ -647,8 +648,9 @@ int gemm_bf16_tn_fused(const void* X, const void* W, void* out, int M, int N, in
   switch (bn) {
     case 16: return launch_gemm<16, 6>(tma, tmb, a, pdl, stream);
     case 32: return launch_gemm<32, 5>(tma, tmb, a, pdl, stream);
-    case 64: return launch_gemm<64, 8>(tma, tmb, a, pdl, stream);
-    case 128: return launch_gemm<128, 6>(tma, tmb, a, pdl, stream);
+    case 64: return launch_gemm<64, 4>(tma, tmb, a, pdl, stream);   // decode, 33-64 rows: two CTAs per SM
+    case 128: return swap ? launch_gemm<128, 3>(tma, tmb, a, pdl, stream)  // decode, 65-128 rows: two CTAs per SM
+                          : launch_gemm<128, 6>(tma, tmb, a, pdl, stream);
     default: return launch_gemm<256, 4>(tma, tmb, a, pdl, stream);
   }
 }
