@@ -39,7 +39,11 @@ def test_header_cites_reference_or_says_no_counterpart():
 
 
 def test_host_only_entry_points_work_without_gpu(so):
-    assert so.bcg_gemm_splits_for(10, 34816, 5120) == 1          # 272 tiles >= 148 SMs
+    assert so.bcg_gemm_splits_for(10, 34816, 5120) == 1          # 272 tiles fill the 296 work slots
+    # Qwen3-14B decode: every projection is ONE wave of one-item CTAs on 2 x 148 slots
+    for n, k in [(7168, 5120), (5120, 5120), (34816, 5120), (5120, 17408)]:
+        items = -(-n // 128) * so.bcg_gemm_splits_for(10, n, k)
+        assert 0.9 * 296 <= items <= 296, (n, k, items)
     assert so.bcg_gemm_splits_for(10, 5120, 5120) > 1
     assert so.bcg_gemm_splits_for(300, 5120, 5120) == 1          # prefill never splits
     # splits depend on (N, K) only -> batch-invariant decode arithmetic
