@@ -518,8 +518,8 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmA
 // round-robin to the 296 work slots of the decode configuration (two CTAs per SM); the factor is
 // chosen to fill whole waves (e.g. 40 tiles x 7 = 280 items = 0.95 wave, every CTA one item,
 // instead of 40 x 8 = 320 = 1.08 waves -> 54 %), discounted by the fp32 partial traffic it adds
-// (4*s*16/K of the weight bytes at 16 rows).  Batches of 33-128 rows (one CTA per SM) use the
-// same factors.
+// (4*s*16/K of the weight bytes at 16 rows).  Batches of 33-128 rows (wider tiles, shorter rings,
+// still two CTAs per SM) use the same factors.
 int gemm_splits_for(int M, int N, int K) {
   if (M > 128) return 1;
   const int tiles = (N + kBlockA - 1) / kBlockA;
