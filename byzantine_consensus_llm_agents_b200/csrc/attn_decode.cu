@@ -144,6 +144,10 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
   const int g = lane >> 2, t = lane & 3;
   const int seq_len = seq_lens[b];
   const int n_splits = (seq_len + kSplitTokens - 1) / kSplitTokens;
+  // A row longer than 256 * max_splits tokens would never see its last chunk arrive: the output
+  // would stay unwritten and the row's chunk counter non-zero (fatal for the shared counters of
+  // bcg_decode_attn_paged_static).  Fail the launch instead of computing a silent wrong answer.
+  if (n_splits > max_splits) __trap();
   const bool live = split < n_splits;
   const int tok0 = split * kSplitTokens;
   const int tok1 = min(seq_len, tok0 + kSplitTokens);
@@ -625,12 +629,8 @@ static int launch_decode(const void* q, const void* kv_cache, const int* block_t
                          int* counters, void* out, int B, int n_heads, int n_kv_heads,
                          int max_splits, float scale, const RopeFusion& rf, cudaStream_t stream) {
   constexpr int SMEM = kAttnStages * kAttnStageBytes + 1024;
-  static bool configured = false;
-  if (!configured) {
-    BCG_CUDA_CHECK(cudaFuncSetAttribute(decode_attn_kernel<G, FUSED>,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-    configured = true;
-  }
+  if (const int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(decode_attn_kernel<G, FUSED>), SMEM))
+    return rc;
   // The layer's cache as a [token-rows, 128] bf16 tensor; the row count only bounds TMA's
   // out-of-range check, the block table never points past the real allocation.
   CUtensorMap kv_map;

@@ -216,12 +216,7 @@ int prefill_attn_paged(const void* q, const void* kv_cache, const int* block_tab
     return BCG_ERR_UNSUPPORTED;
   }
   constexpr int SMEM = 16384 * 5;
-  static bool configured = false;
-  if (!configured) {
-    BCG_CUDA_CHECK(cudaFuncSetAttribute(prefill_attn_kernel,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-    configured = true;
-  }
+  if (const int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(prefill_attn_kernel), SMEM)) return rc;
   prefill_attn_kernel<<<dim3(n_tiles, n_heads), 128, SMEM, stream>>>(
       reinterpret_cast<const __nv_bfloat16*>(q), reinterpret_cast<const __nv_bfloat16*>(kv_cache),
       block_table, max_blocks_per_seq, tile_info, reinterpret_cast<__nv_bfloat16*>(out), n_heads,

@@ -17,14 +17,39 @@ int& launch_flags() {
   return flags;
 }
 
+// Function attributes belong to the (kernel, device) pair, not to the kernel: a process that drives
+// several GPUs (bcg_decode_attn_paged_static documents that use) must set them once on EACH device.
+static bool first_use_on_current_device(std::unordered_set<unsigned long long>& done, const void* kernel) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) dev = 0;
+  // kernel addresses are at least 4-byte aligned in practice; fold the ordinal into the high bits
+  const unsigned long long key = reinterpret_cast<unsigned long long>(kernel) ^
+                                 (static_cast<unsigned long long>(dev + 1) << 56);
+  return done.insert(key).second;
+}
+
 void prefer_max_smem_carveout(const void* kernel) {
   static std::mutex mu;
-  static std::unordered_set<const void*> done;
+  static std::unordered_set<unsigned long long> done;
   std::lock_guard<std::mutex> lock(mu);
-  if (done.insert(kernel).second &&
+  if (first_use_on_current_device(done, kernel) &&
       cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
                            cudaSharedmemCarveoutMaxShared) != cudaSuccess)
     (void)cudaGetLastError();  // a hint; failing to set it is harmless
+}
+
+int ensure_dynamic_smem(const void* kernel, int bytes) {
+  static std::mutex mu;
+  static std::unordered_set<unsigned long long> done;
+  std::lock_guard<std::mutex> lock(mu);
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) dev = 0;
+  const unsigned long long key = reinterpret_cast<unsigned long long>(kernel) ^
+                                 (static_cast<unsigned long long>(dev + 1) << 56);
+  if (done.count(key)) return BCG_OK;
+  BCG_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  done.insert(key);
+  return BCG_OK;
 }
 
 void set_last_error(const char* what, const char* detail) {

@@ -43,6 +43,8 @@ int& launch_flags();
 // dependent launch it would start only after they exit — and so would ITS dependents.  Every
 // kernel launched through launch_k therefore asks for the same maximum carve-out (once).
 void prefer_max_smem_carveout(const void* kernel);
+// Raises the kernel's dynamic shared-memory limit on the CURRENT device (once per kernel and device).
+int ensure_dynamic_smem(const void* kernel, int bytes);
 
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,

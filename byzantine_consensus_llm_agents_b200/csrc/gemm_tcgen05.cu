@@ -491,12 +491,8 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmA
                        cudaStream_t stream) {
   constexpr int STAGE_BYTES = kBlockA * kBlockK * 2 + BN * kBlockK * 2;
   constexpr int SMEM = STAGES * STAGE_BYTES + 1024 + 256;
-  static bool configured = false;
-  if (!configured) {
-    BCG_CUDA_CHECK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, STAGES>,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-    configured = true;
-  }
+  if (const int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(gemm_tcgen05_kernel<BN, STAGES>), SMEM))
+    return rc;
   const int total = a.tiles_a * a.tiles_b * a.splits;
   cudaLaunchConfig_t cfg = {};
   const int slots = two_cta(BN, STAGES) ? 2 * num_sms() : num_sms();

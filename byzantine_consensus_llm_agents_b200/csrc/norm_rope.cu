@@ -508,12 +508,9 @@ int add_rmsnorm(float* residual, const void* delta, int delta_is_f32, int n_part
                             stream, residual, delta, delta_is_f32, n_partials, partial_stride, w,
                             reinterpret_cast<__nv_bfloat16*>(xn), src_rows, d, eps));
   } else {
-    static bool configured = false;
-    if (!configured) {
-      BCG_CUDA_CHECK(cudaFuncSetAttribute(add_rmsnorm_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          kNormSegments * kSegThreads * kSegTurns * 16));
-      configured = true;
-    }
+    if (const int rc = ensure_dynamic_smem(reinterpret_cast<const void*>(add_rmsnorm_row_kernel),
+                                           kNormSegments * kSegThreads * kSegTurns * 16))
+      return rc;
     BCG_CUDA_CHECK(launch_k(add_rmsnorm_row_kernel, dim3(T), dim3(kRowThreads), static_cast<size_t>(d) * 4,
                             stream, residual, delta, delta_is_f32, n_partials, partial_stride, w,
                             reinterpret_cast<__nv_bfloat16*>(xn), src_rows, d, eps));

@@ -380,6 +380,9 @@ def ast_to_dfa(ast) -> Tuple[np.ndarray, np.ndarray]:
                 remap[int(part[t])] = len(remap)
                 queue.append(int(part[t]))
     n = len(remap)
+    if n > 32767:
+        # the device tables (and the sampler's DFA walk) hold states as int16
+        raise UnsupportedSchema(f"schema compiles to {n} DFA states; the device tables hold at most 32767")
     out = np.full((n, 256), -1, np.int16)
     acc = np.zeros(n, bool)
     for c, i2 in remap.items():

@@ -72,7 +72,8 @@ PRESETS = {
     "qwen3-8b": ModelConfig("qwen3-8b", 36, 4096, 32, 8, 12288, 151936),
     "qwen3-14b": ModelConfig("qwen3-14b", 40, 5120, 40, 8, 17408, 151936),
     "qwen3-32b": ModelConfig("qwen3-32b", 64, 5120, 64, 8, 25600, 151936),
-    "mistral-22b": ModelConfig("mistral-22b", 56, 6144, 48, 8, 16384, 32768, qk_norm=False,
+    # Mistral-Small-Instruct-2409's config.json: rms_norm_eps 1e-05 (Qwen3's is 1e-06)
+    "mistral-22b": ModelConfig("mistral-22b", 56, 6144, 48, 8, 16384, 32768, rms_eps=1e-5, qk_norm=False,
                                family="mistral"),
 }
 
@@ -102,6 +103,69 @@ def rope_table(cfg: ModelConfig, device) -> torch.Tensor:
     pos = torch.arange(cfg.max_pos, dtype=torch.float32)
     freqs = pos[:, None] * inv_freq[None, :]
     return torch.cat([freqs.cos(), freqs.sin()], dim=1).contiguous().to(device)
+
+
+def _i64(x: int) -> int:
+    """Two's-complement view of a 64-bit constant (torch has no uint64 arithmetic)."""
+    x &= 0xFFFFFFFFFFFFFFFF
+    return x - (1 << 64) if x >= (1 << 63) else x
+
+
+def _lsr(x: torch.Tensor, k: int) -> torch.Tensor:
+    """Logical shift right of int64 lanes (torch's >> is arithmetic)."""
+    return (x >> k) & ((1 << (64 - k)) - 1)
+
+
+def _splitmix64(x: torch.Tensor) -> torch.Tensor:
+    x = x + _i64(0x9E3779B97F4A7C15)
+    x = (x ^ _lsr(x, 30)) * _i64(0xBF58476D1CE4E5B9)
+    x = (x ^ _lsr(x, 27)) * _i64(0x94D049BB133111EB)
+    return x ^ _lsr(x, 31)
+
+
+def hashed_normal(rows: int, cols: int, seed: int, tensor_id: int, device, std: float = 0.02,
+                  row0: int = 0, n_rows: int = None) -> torch.Tensor:
+    """bf16 [n_rows, cols] slice (rows row0..) of a pseudo-normal N(0, std) matrix that is a pure
+    function of (seed, tensor_id, row, col) and BIT-IDENTICAL on every device: element (r, c) hashes
+    the counter r*cols+c with splitmix64 under two keys, sums the eight 16-bit fields (Irwin-Hall,
+    integer arithmetic only), and scales the centred integer by one fp32 multiply.  Lets a CPU
+    oracle stream a full-depth model layer by layer over exactly the weights a GPU holds, without
+    either side storing or shipping them (tests/test_gpu_model.py full-depth check)."""
+    n_rows = rows - row0 if n_rows is None else n_rows
+    out = torch.empty(n_rows, cols, dtype=torch.bfloat16, device=device)
+    key = _i64(seed * 0xD1342543DE82EF95 + tensor_id * 0xA0761D6478BD642F + 0x2545F4914F6CDD1D)
+    scale = std / (8.0 * (2.0 ** 32 - 1.0) / 12.0) ** 0.5      # eight uniform 16-bit fields
+    chunk = max(1, (1 << 24) // cols)
+    for r in range(0, n_rows, chunk):
+        m = min(chunk, n_rows - r)
+        idx = torch.arange((row0 + r) * cols, (row0 + r + m) * cols, dtype=torch.int64, device=device)
+        tot = torch.zeros_like(idx)
+        for k in (0, 1):
+            h = _splitmix64(idx ^ (key + k * _i64(0x632BE59BD9B4E019)))
+            for sh in (0, 16, 32, 48):
+                tot += _lsr(h, sh) & 0xFFFF
+        tot -= 4 * 0xFFFF
+        out[r:r + m] = (tot.to(torch.float32) * scale).view(m, cols).to(torch.bfloat16)
+    return out
+
+
+# HF parameter names of one decoder layer and the ids hashed_normal draws them under
+_HASHED_LAYER_TENSORS = ("self_attn.q_proj", "self_attn.k_proj", "self_attn.v_proj", "self_attn.o_proj",
+                         "mlp.gate_proj", "mlp.up_proj", "mlp.down_proj")
+
+
+def hashed_state_dict_layer(cfg: "ModelConfig", layer: int, seed: int, device) -> dict:
+    """transformers-named bf16 weights of decoder layer `layer` under the hashed init."""
+    d, hd = cfg.d_model, cfg.head_dim
+    shapes = {"self_attn.q_proj": (cfg.n_heads * hd, d), "self_attn.k_proj": (cfg.n_kv_heads * hd, d),
+              "self_attn.v_proj": (cfg.n_kv_heads * hd, d), "self_attn.o_proj": (d, cfg.n_heads * hd),
+              "mlp.gate_proj": (cfg.d_ff, d), "mlp.up_proj": (cfg.d_ff, d), "mlp.down_proj": (d, cfg.d_ff)}
+    return {name: hashed_normal(*shapes[name], seed, 16 * (layer + 1) + j, device)
+            for j, name in enumerate(_HASHED_LAYER_TENSORS)}
+
+
+def hashed_embed(cfg: "ModelConfig", seed: int, device, which: str = "embed") -> torch.Tensor:
+    return hashed_normal(cfg.vocab, cfg.d_model, seed, 1 if which == "embed" else 2, device)
 
 
 def interleave_gate_up(gate: torch.Tensor, up: torch.Tensor) -> torch.Tensor:
@@ -212,6 +276,30 @@ class Weights:
             if cfg.qk_norm:
                 w.q_norm.append(ones(hd))
                 w.k_norm.append(ones(hd))
+        w.cos_sin = rope_table(cfg, device)
+        return w
+
+    @staticmethod
+    def hashed_init(cfg: ModelConfig, device, seed: int = 0) -> "Weights":
+        """Full model under the device-independent hashed init (hashed_normal): norm weights 1, every
+        matrix a pure function of (seed, tensor, row, col).  Generated on the device, one layer at a
+        time; a CPU process can regenerate any layer bit for bit (oracle/tools/make_full_depth_golden.py)."""
+        ones = lambda n: torch.ones(n, dtype=torch.float32, device=device)
+        embed = hashed_embed(cfg, seed, device)
+        lm = embed if cfg.tie_embeddings else hashed_embed(cfg, seed, device, "lm_head")
+        w = Weights(cfg, embed, lm, ones(cfg.d_model))
+        for l in range(cfg.n_layers):
+            sd = hashed_state_dict_layer(cfg, l, seed, device)
+            w.ln1.append(ones(cfg.d_model))
+            w.ln2.append(ones(cfg.d_model))
+            w.w_qkv.append(torch.cat([sd["self_attn.q_proj"], sd["self_attn.k_proj"], sd["self_attn.v_proj"]]))
+            w.w_o.append(sd["self_attn.o_proj"])
+            w.w_gate_up.append(interleave_gate_up(sd["mlp.gate_proj"], sd["mlp.up_proj"]).contiguous())
+            w.w_down.append(sd["mlp.down_proj"])
+            if cfg.qk_norm:
+                w.q_norm.append(ones(cfg.head_dim))
+                w.k_norm.append(ones(cfg.head_dim))
+            del sd
         w.cos_sin = rope_table(cfg, device)
         return w
 

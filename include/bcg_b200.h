@@ -129,7 +129,8 @@ int bcg_swiglu_reduce(const float* partials, int n_partials, long long partial_s
  * scratch_ml: B*n_heads*max_splits*2 floats; chunk_counters: B*n_kv_heads int32 that must be
  * ZERO before the first call and that every call leaves zero again (keep them in a buffer of
  * their own: partial results written by a call of another shape must never land on them);
- * max_splits >= ceil(max seq_len / 256).
+ * max_splits >= ceil(max seq_len / 256) — a longer row makes the kernel trap (the launch fails with
+ * a CUDA error) rather than leave its output unwritten.
  * Stands in for the FlashInfer paged decode kernel vLLM dispatches on sm_100. */
 int bcg_decode_attn_paged(const void* q, const void* kv_cache, const int* block_table,
                           int max_blocks_per_seq, const int* seq_lens, void* out, float* scratch_o,
@@ -160,7 +161,8 @@ int bcg_decode_attn_paged_qkv(const float* qkv, int n_partials, long long partia
  * must avoid cudaMalloc/cudaFree because they synchronise the device.  The scratch is a 16 MiB
  * array inside the library (held by every GPU that loads it, until exit), so the problem must
  * satisfy B * n_heads * max_splits * 130 <= 4 * 1024 * 1024 floats and B * n_kv_heads <= 4096;
- * larger calls return BCG_STATUS_TOO_LARGE.  The first call on a device resolves the array's address — make it
+ * larger calls return BCG_STATUS_TOO_LARGE, and every seq_lens[b] must be <= 256 * max_splits (a longer
+ * row traps, as above).  The first call on a device resolves the array's address — make it
  * before any stream capture.  Calls share the array: keep them on one stream (overlapping calls
  * race); the caller never has to clear anything (the chunk counters inside start at zero and every
  * call returns them to zero).  Allocates nothing, frees nothing. */

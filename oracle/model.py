@@ -48,3 +48,21 @@ def full_logits(model, ids) -> torch.Tensor:
     """fp32 logits [T, V] for one sequence (no cache)."""
     out = model(input_ids=torch.tensor([list(ids)], dtype=torch.long), use_cache=False)
     return out.logits[0].float()
+
+
+def build_hf_model_hashed(cfg, seed: int = 0):
+    """Whole transformers model holding the device-independent hashed init
+    (byzantine_consensus_llm_agents_b200.model.hashed_normal) — the same parameter values
+    `Weights.hashed_init` puts on the GPU; norm weights stay 1.  For models that fit in host memory;
+    larger ones are streamed layer by layer (oracle/tools/make_full_depth_golden.py)."""
+    from byzantine_consensus_llm_agents_b200 import model as M
+    model = build_hf_model(cfg, seed=0)
+    with torch.no_grad():
+        model.model.embed_tokens.weight.copy_(M.hashed_embed(cfg, seed, "cpu").float())
+        if not cfg.tie_embeddings:
+            model.lm_head.weight.copy_(M.hashed_embed(cfg, seed, "cpu", "lm_head").float())
+        for l, layer in enumerate(model.model.layers):
+            for name, w in M.hashed_state_dict_layer(cfg, l, seed, "cpu").items():
+                a, b = name.split(".")
+                getattr(getattr(layer, a), b).weight.copy_(w.float())
+    return model

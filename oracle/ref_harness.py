@@ -137,7 +137,8 @@ def import_reference(adapter_module: Optional[types.ModuleType] = None):
 
 def run_game(ref, num_honest: int, num_byzantine: int, max_rounds: int, seed: int = 1234,
              greedy: bool = False, awareness: str = "may_exist", model_name: Optional[str] = None,
-             model_config_overrides: Optional[dict] = None, quiet: bool = True):
+             model_config_overrides: Optional[dict] = None, quiet: bool = True,
+             llm_overrides: Optional[dict] = None):
     """One BCGSimulation run of the unmodified reference in a scratch cwd.  Returns
     (statistics dict, round-by-round transcript, simulation object)."""
     cfg = ref.config
@@ -148,6 +149,8 @@ def run_game(ref, num_honest: int, num_byzantine: int, max_rounds: int, seed: in
     if greedy:
         cfg.LLM_CONFIG["temperature_decide"] = 0.0
         cfg.LLM_CONFIG["temperature_vote"] = 0.0
+    if llm_overrides:          # e.g. shorter max_tokens for wide, CPU-expensive parity fixtures
+        cfg.LLM_CONFIG.update(llm_overrides)
     cfg.METRICS_CONFIG["save_results"] = False
     random.seed(seed)
     cwd = os.getcwd()

@@ -39,6 +39,9 @@ def main():
     ap.add_argument("--game-seed", type=int, default=1234)
     ap.add_argument("--weight-seed", type=int, default=0)
     ap.add_argument("--temperature", default="greedy", help="'greedy' or 'shipped' (0.5 / 0.3)")
+    ap.add_argument("--max-tokens-decide", type=int, default=None,
+                    help="override LLM_CONFIG['max_tokens_decide'] (config.py:52-58; data change only)")
+    ap.add_argument("--max-tokens-vote", type=int, default=None)
     ap.add_argument("--out", required=True)
     a = ap.parse_args()
 
@@ -55,7 +58,10 @@ def main():
     t0 = time.time()
     stats, transcript, sim = H.run_game(ref, a.honest, a.byzantine, a.rounds, seed=a.game_seed,
                                         greedy=(a.temperature == "greedy"), awareness=a.awareness,
-                                        model_name=HF_NAME.get(a.model, a.model))
+                                        model_name=HF_NAME.get(a.model, a.model),
+                                        llm_overrides={k: v for k, v in (("max_tokens_decide", a.max_tokens_decide),
+                                                                         ("max_tokens_vote", a.max_tokens_vote))
+                                                       if v is not None})
     wall = time.time() - t0
     # de-duplicate identical (prompt, schema, max_tokens, temperature) generations
     uniq, calls = {}, []
@@ -80,6 +86,7 @@ def main():
         "meta": {"model": a.model, "layers": cfg.n_layers, "vocab": cfg.vocab, "honest": a.honest,
                  "byzantine": a.byzantine, "rounds": a.rounds, "awareness": a.awareness,
                  "game_seed": a.game_seed, "weight_seed": a.weight_seed, "temperature": a.temperature,
+                 "max_tokens_decide": a.max_tokens_decide, "max_tokens_vote": a.max_tokens_vote,
                  "oracle_wall_s": round(wall, 1), "oracle_stats": eng.stats,
                  "generator": "oracle/tools/make_game_golden.py"},
         "requests": sorted(uniq.values(), key=lambda r: r["id"]),

@@ -7,11 +7,12 @@ a fixed 16 MiB device array of its own instead.
 
 The test calls the entry point through the C ABI twice in a row — the second time on a different,
 shorter batch, so anything stale left in the shared array by the first call would show — and
-compares each result with the existing caller-scratch entry point.  Both run the same kernels, so
-the outputs are expected to be identical; the assertion uses the 2e-2 tolerance of the other
-decode-attention tests.  Collected last on purpose (file name): a run that stops at the first
-failure has then already run every other test.  It needs no state from other tests and passes in
-a fresh process as well.
+checks each result two ways: bit for bit against the existing caller-scratch entry point (both run
+the same kernels in the same order, so nothing short of equality is acceptable), and — so that the
+check does not rest on a sibling alone — against an fp32 softmax(QK^T)V computed by torch over the
+gathered pages, within the 2e-2 tolerance of the other decode-attention tests.  Collected last on
+purpose (file name): a run that stops at the first failure has then already run every other test.
+It needs no state from other tests and passes in a fresh process as well.
 """
 import math
 
@@ -61,19 +62,53 @@ def _run_both(lib, lens, H, HKV, seed):
                                              seq.data_ptr(), got.data_ptr(), B, H, HKV, 16, max_splits,
                                              scale, L.stream_ptr()))
     torch.cuda.synchronize()
-    return want.float(), got.float()
+    return want.float(), got.float(), _fp32_reference(q, cache, bt, lens, H, HKV)
+
+
+def _fp32_reference(q, cache, bt, lens, H, HKV):
+    """softmax(q K^T / sqrt(128)) V per row in fp32, K/V gathered from the pages by the block table."""
+    G = H // HKV
+    out = torch.empty(len(lens), H * 128, device=q.device)
+    for b, n in enumerate(lens):
+        pages = bt[b, :(n + 15) // 16].long()
+        kv = cache[pages].float()                                   # [P, 2, HKV, 16, 128]
+        K = kv[:, 0].permute(1, 0, 2, 3).reshape(HKV, -1, 128)[:, :n]
+        V = kv[:, 1].permute(1, 0, 2, 3).reshape(HKV, -1, 128)[:, :n]
+        qb = q[b].float().view(HKV, G, 128)
+        p = torch.softmax(torch.einsum("kgd,ksd->kgs", qb, K) / math.sqrt(128), dim=-1)
+        out[b] = torch.einsum("kgs,ksd->kgd", p, V).reshape(-1)
+    return out
 
 
 def test_static_scratch_matches_caller_scratch_on_two_calls_in_a_row():
     lib = L.load()
     # call 1: long rows fill many chunks of the shared array
-    want, got = _run_both(lib, [2000, 1300, 257, 40], 40, 8, seed=1)
+    want, got, ref = _run_both(lib, [2000, 1300, 257, 40], 40, 8, seed=1)
     assert torch.isfinite(got).all()
-    assert (want - got).abs().max().item() <= TOL
+    assert torch.equal(want, got)
+    assert (got - ref).abs().max().item() <= TOL
     # call 2: fewer, shorter rows and another head layout reuse the same (now dirty) array
-    want, got = _run_both(lib, [17, 300], 16, 8, seed=2)
+    want, got, ref = _run_both(lib, [17, 300], 16, 8, seed=2)
     assert torch.isfinite(got).all()
-    assert (want - got).abs().max().item() <= TOL
+    assert torch.equal(want, got)
+    assert (got - ref).abs().max().item() <= TOL
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_static_scratch_on_a_second_device():
+    """The array's address and the kernel's shared-memory limit are per device: a process that
+    drives two GPUs must be able to make its first call on cuda:1 after having used cuda:0."""
+    global DEV
+    lib = L.load()
+    _run_both(lib, [300, 40], 16, 8, seed=4)                 # cuda:0 first
+    DEV = "cuda:1"
+    try:
+        with torch.cuda.device(1):
+            want, got, ref = _run_both(lib, [700, 17, 256], 40, 8, seed=5)
+            assert torch.equal(want, got)
+            assert (got - ref).abs().max().item() <= TOL
+    finally:
+        DEV = "cuda"
 
 
 def test_static_scratch_rejects_oversized_problems():
