@@ -157,9 +157,10 @@ int bcg_decode_attn_paged_static(const void* q, const void* kv_cache, const int*
 
 int bcg_prefill_attn_paged(const void* q, const void* kv_cache, const int* block_table,
                            int max_blocks_per_seq, const int* tile_info, int n_tiles, void* out,
-                           int n_heads, int n_kv_heads, int page_size, float scale, void* stream) {
+                           int n_q_rows, int n_heads, int n_kv_heads, int page_size, float scale,
+                           void* stream) {
   return prefill_attn_paged(q, kv_cache, block_table, max_blocks_per_seq, tile_info, n_tiles, out,
-                            n_heads, n_kv_heads, page_size, scale, S(stream));
+                            n_q_rows, n_heads, n_kv_heads, page_size, scale, S(stream));
 }
 
 int bcg_mask_sample(const bcg_sampler_args* args, void* stream) {
@@ -169,6 +170,16 @@ int bcg_mask_sample(const bcg_sampler_args* args, void* stream) {
 int bcg_tp_unique_id(void* out_128_bytes) { return tp_unique_id(out_128_bytes); }
 int bcg_tp_init(const void* id_128_bytes, int rank, int size) { return tp_init(id_128_bytes, rank, size); }
 int bcg_tp_shutdown(void) { return tp_shutdown(); }
+long long bcg_tp_symm_bytes_for(long long region_floats, int size) {
+  if (region_floats < 0 || size < 1) return 0;
+  return 4 * (tp_symm_flag_floats() + 2 * static_cast<long long>(size) * region_floats);
+}
+int bcg_tp_add_norm_stats(float* residual, const float* partials, int n_partials, long long partial_stride,
+                          const float* w, void* xn, float* sumsq, int slot, long long region_floats, int T,
+                          int d, void* stream) {
+  return tp_add_norm_stats(residual, partials, n_partials, partial_stride, w, xn, sumsq, slot, region_floats,
+                           T, d, S(stream));
+}
 int bcg_tp_symm_create(long long bytes, void* handle_out_64_bytes) {
   void* local = nullptr;
   return tp_symm_create(bytes, handle_out_64_bytes, &local);

@@ -54,7 +54,7 @@ int decode_attn_paged_static(const void* q, const void* kv_cache, const int* blo
                              cudaStream_t stream);
 int prefill_attn_paged(const void* q, const void* kv_cache, const int* block_table,
                        int max_blocks_per_seq, const int* tile_info, int n_tiles, void* out,
-                       int n_heads, int n_kv_heads, int page_size, float scale,
+                       int n_q_rows, int n_heads, int n_kv_heads, int page_size, float scale,
                        cudaStream_t stream);
 
 int mask_sample(const bcg_sampler_args* a, cudaStream_t stream);
@@ -72,10 +72,10 @@ int tp_symm_open(const void* handles, int rank, int size);
 void* tp_symm_local();
 void* const* tp_symm_peers_device();
 long long tp_symm_bytes();
-// fused cross-GPU reduction + residual add + RMSNorm over peer memory (tp_reduce_norm.cu)
-int tp_signal(int slot, cudaStream_t stream);
-int tp_add_rmsnorm(float* residual, long long region_offset_floats, int n_partials, long long partial_stride,
-                   const float* w, void* xn, int slot, int T, int d, float eps, cudaStream_t stream);
+// fused cross-GPU reduction + residual add + RMSNorm statistics over peer memory (tp_reduce_norm.cu)
+int tp_add_norm_stats(float* residual, const float* partials, int n_partials, long long partial_stride,
+                      const float* w, void* xn, float* sumsq, int slot, long long region_floats, int T,
+                      int d, cudaStream_t stream);
 long long tp_symm_flag_floats();
 
 }  // namespace bcg

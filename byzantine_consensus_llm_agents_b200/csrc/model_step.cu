@@ -37,8 +37,8 @@ int model_prefill(const bcg_model* m, const bcg_workspace* ws, const int* ids, c
   const int qkv_dim = (hq + 2 * hkv) * 128;
   const float scale = 0.08838834764831845f;  // 1/sqrt(128)
   const int tp = m->tp_size > 1 ? m->tp_size : 1;
-  if (tp > 1 && (tp_size() != tp || !ws->logits_local)) {
-    set_last_error("bcg_model_prefill", "tp_size does not match bcg_tp_init, or logits_local missing");
+  if (tp > 1 && tp_size() != tp) {
+    set_last_error("bcg_model_prefill", "tp_size does not match bcg_tp_init");
     return BCG_ERR_ARG;
   }
   for (int l = 0; l < m->n_layers; ++l) {
@@ -55,7 +55,7 @@ int model_prefill(const bcg_model* m, const bcg_workspace* ws, const int* ids, c
                                 m->k_norm ? m->k_norm[l] : nullptr, m->cos_sin, positions, slot_map,
                                 ws->q, m->kv_cache[l], T, hq, hkv, m->page_size, m->rms_eps, st));
     BCG_TRY(prefill_attn_paged(ws->q, m->kv_cache[l], block_table, max_blocks, tile_info, n_tiles,
-                               ws->attn, hq, hkv, m->page_size, scale, st));
+                               ws->attn, T, hq, hkv, m->page_size, scale, st));
     BCG_TRY(gemm_bf16_tn(ws->attn, m->w_o[l], ws->delta, T, d, hq * 128, hq * 128, hq * 128, d,
                          BCG_EPI_F32, 1, 0, st));
     if (tp > 1) BCG_TRY(tp_all_reduce_f32(ws->delta, static_cast<long long>(T) * d, st));
@@ -69,15 +69,10 @@ int model_prefill(const bcg_model* m, const bcg_workspace* ws, const int* ids, c
   }
   BCG_TRY(add_rmsnorm(ws->residual, ws->delta, 1, 1, 0, m->final_norm, ws->xn_last, last_rows,
                       n_seqs, d, m->rms_eps, st));
-  if (tp > 1) {
-    // vocab-parallel head: local [n_seqs, V/tp] logits, all-gathered rank-major
-    BCG_TRY(gemm_bf16_tn(ws->xn_last, m->lm_head, ws->logits_local, n_seqs, m->vocab, d, d, d, m->vocab,
-                         BCG_EPI_F32, 1, 0, st));
-    BCG_TRY(tp_all_gather_f32(ws->logits_local, ws->logits, static_cast<long long>(n_seqs) * m->vocab, st));
-  } else {
-    BCG_TRY(gemm_bf16_tn(ws->xn_last, m->lm_head, ws->logits, n_seqs, m->vocab, d, d, d, m->vocab,
-                         BCG_EPI_F32, 1, 0, st));
-  }
+  // With tensor parallelism m->vocab is this rank's shard and the logits stay sharded: the sampler
+  // exchanges one candidate per row instead (bcg_sampler_args.tp_size).
+  BCG_TRY(gemm_bf16_tn(ws->xn_last, m->lm_head, ws->logits, n_seqs, m->vocab, d, d, d, m->vocab,
+                       BCG_EPI_F32, 1, 0, st));
   return BCG_OK;
 }
 
@@ -109,21 +104,18 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
     return BCG_ERR_TOO_LARGE;
   }
   const int tp = m->tp_size > 1 ? m->tp_size : 1;
-  if (tp > 1 && (tp_size() != tp || !ws->logits_local)) {
-    set_last_error("bcg_model_decode", "tp_size does not match bcg_tp_init, or logits_local missing");
+  if (tp > 1 && tp_size() != tp) {
+    set_last_error("bcg_model_decode", "tp_size does not match bcg_tp_init");
     return BCG_ERR_ARG;
   }
-  // fused peer-memory all-reduce (tp_reduce_norm.cu) when the symmetric buffer is set up
-  const bool fused = tp > 1 && ws->tp_region_floats > 0 && tp_symm_local() != nullptr;
-  float* sym = static_cast<float*>(tp_symm_local());
-  const long long off_o = tp_symm_flag_floats(), off_dn = tp_symm_flag_floats() + ws->tp_region_floats;
-  if (fused) {
-    const long long need_sym = static_cast<long long>(s_o > s_dn ? s_o : s_dn) * B * d;
-    if (need_sym > ws->tp_region_floats ||
-        (tp_symm_flag_floats() + 2 * ws->tp_region_floats) * 4 > tp_symm_bytes()) {
-      set_last_error("bcg_model_decode", "symmetric TP buffer too small");
-      return BCG_ERR_TOO_LARGE;
-    }
+  // Tensor parallelism, fused path (tp_reduce_norm.cu) when the symmetric buffer has data regions:
+  // the all-reduce after each row-parallel projection happens inside the norm-statistics kernel
+  // that follows it (local slab sum -> push over NVLink -> flags -> rank-ordered sum), and 1/RMS is
+  // applied by the next projection's epilogue.  Otherwise NCCL all-reduces + complete norm kernels.
+  const bool fused = tp > 1 && ws->tp_region_floats > 0 && tp_symm_local() != nullptr && ws->row_sumsq;
+  if (fused && static_cast<long long>(B) * d > ws->tp_region_floats) {
+    set_last_error("bcg_model_decode", "symmetric TP buffer too small");
+    return BCG_ERR_TOO_LARGE;
   }
   const int gf = flags & BCG_GEMM_PDL;
   // profiling aids (tools/step_ablation.py): leave one kernel family out of the step to read its
@@ -151,7 +143,8 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
   // residual and writes bf16(residual * w) + 8 segment sums per row; the projection that follows
   // applies 1/RMS in its epilogue, so the row-wide reduction leaves the critical path.
   const bool dn = !nf && tp == 1 && ws->row_sumsq && B <= 128 && (flags & BCG_STEP_DEFERRED_NORM) && !skip_norm;
-  const int n_tiles_d = dn ? 8 : d / 128;
+  const bool scaled = nf || dn || fused;   // the consuming projection applies 1/RMS in its epilogue
+  const int n_tiles_d = (dn || fused) ? 8 : d / 128;
   const int table_floats = (d / 128 > 8 ? d / 128 : 8) * 128;
   float* sumsq_attn = ws->row_sumsq;                      // written after o, read by gate_up
   float* sumsq_mlp = ws->row_sumsq ? ws->row_sumsq + table_floats : nullptr;  // after down -> qkv / lm_head
@@ -181,8 +174,8 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
       BCG_TRY(add_norm_stats(ws->residual, P, 1, s_dn, static_cast<long long>(B) * d, m->ln1[l], ws->xn,
                              sumsq_mlp, B, d, st));
     } else if (fused) {
-      BCG_TRY(tp_add_rmsnorm(ws->residual, off_dn, s_dn, static_cast<long long>(B) * d, m->ln1[l], ws->xn, 1,
-                             B, d, m->rms_eps, st));
+      BCG_TRY(tp_add_norm_stats(ws->residual, P, s_dn, static_cast<long long>(B) * d, m->ln1[l], ws->xn,
+                                sumsq_mlp, 1, ws->tp_region_floats, B, d, st));
     } else if (!skip_norm) {
       BCG_TRY(add_rmsnorm(ws->residual, P, 1, s_dn, static_cast<long long>(B) * d, m->ln1[l], ws->xn,
                           nullptr, B, d, m->rms_eps, st));
@@ -190,7 +183,7 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
     if (!skip_qkv) {
       const bcg_gemm_fusion f = consumer(sumsq_mlp);
       BCG_TRY(gemm_bf16_tn_fused(ws->xn, m->w_qkv[l], P, B, qkv_dim, d, d, d, qkv_dim, BCG_EPI_F32, s_qkv,
-                                 gf, ((nf || dn) && l > 0) ? &f : nullptr, st));
+                                 gf, (scaled && l > 0) ? &f : nullptr, st));
     }
     if (fuse_rope) {
       if (!skip_attn)
@@ -213,13 +206,10 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
                               m->page_size, ws->max_splits, scale, st));
     }
     if (fused) {
-      // row-parallel projection straight into the symmetric buffer; the norm kernel sums every
-      // rank's slabs from peer memory
-      BCG_TRY(gemm_bf16_tn(ws->attn, m->w_o[l], sym + off_o, B, d, hq * 128, hq * 128, hq * 128, d,
-                           BCG_EPI_F32, s_o, gf, st));
-      BCG_TRY(tp_signal(0, st));
-      BCG_TRY(tp_add_rmsnorm(ws->residual, off_o, s_o, static_cast<long long>(B) * d, m->ln2[l], ws->xn, 0, B,
-                             d, m->rms_eps, st));
+      BCG_TRY(gemm_bf16_tn(ws->attn, m->w_o[l], P, B, d, hq * 128, hq * 128, hq * 128, d, BCG_EPI_F32, s_o,
+                           gf, st));
+      BCG_TRY(tp_add_norm_stats(ws->residual, P, s_o, static_cast<long long>(B) * d, m->ln2[l], ws->xn,
+                                sumsq_attn, 0, ws->tp_region_floats, B, d, st));
     } else if (nf) {
       const bcg_gemm_fusion f = producer(sumsq_attn, m->ln2[l], ws->xn);
       if (!skip_o)
@@ -243,15 +233,14 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
     if (skip_gu) {
     } else if (s_gu == 1) {
       BCG_TRY(gemm_bf16_tn_fused(ws->xn, m->w_gate_up[l], ws->act, B, 2 * ff, d, d, d, ff, BCG_EPI_SWIGLU, 1,
-                                 gf, (nf || dn) ? &f_gu : nullptr, st));
+                                 gf, scaled ? &f_gu : nullptr, st));
     } else {
       BCG_TRY(gemm_bf16_tn_fused(ws->xn, m->w_gate_up[l], P, B, 2 * ff, d, d, d, 2 * ff, BCG_EPI_F32, s_gu,
-                                 gf, (nf || dn) ? &f_gu : nullptr, st));
+                                 gf, scaled ? &f_gu : nullptr, st));
       BCG_TRY(swiglu_reduce(P, s_gu, static_cast<long long>(B) * 2 * ff, ws->act, B, 2 * ff, st));
     }
     if (fused) {
-      BCG_TRY(gemm_bf16_tn(ws->act, m->w_down[l], sym + off_dn, B, d, ff, ff, ff, d, BCG_EPI_F32, s_dn, gf, st));
-      BCG_TRY(tp_signal(1, st));
+      BCG_TRY(gemm_bf16_tn(ws->act, m->w_down[l], P, B, d, ff, ff, ff, d, BCG_EPI_F32, s_dn, gf, st));
     } else if (nf) {
       const bool last = (l + 1 == m->n_layers);
       const bcg_gemm_fusion f = producer(sumsq_mlp, last ? m->final_norm : m->ln1[l + 1],
@@ -270,20 +259,17 @@ int model_decode(const bcg_model* m, const bcg_workspace* ws, const int* ids, co
     BCG_TRY(add_norm_stats(ws->residual, P, 1, s_dn, static_cast<long long>(B) * d, m->final_norm,
                            ws->xn_last, sumsq_mlp, B, d, st));
   } else if (fused) {
-    BCG_TRY(tp_add_rmsnorm(ws->residual, off_dn, s_dn, static_cast<long long>(B) * d, m->final_norm,
-                           ws->xn_last, 1, B, d, m->rms_eps, st));
+    BCG_TRY(tp_add_norm_stats(ws->residual, P, s_dn, static_cast<long long>(B) * d, m->final_norm, ws->xn_last,
+                              sumsq_mlp, 1, ws->tp_region_floats, B, d, st));
   } else {
     BCG_TRY(add_rmsnorm(ws->residual, P, 1, s_dn, static_cast<long long>(B) * d, m->final_norm,
                         ws->xn_last, nullptr, B, d, m->rms_eps, st));
   }
-  if (tp > 1) {
-    BCG_TRY(gemm_bf16_tn(ws->xn_last, m->lm_head, ws->logits_local, B, m->vocab, d, d, d, m->vocab,
-                         BCG_EPI_F32, 1, gf, st));
-    BCG_TRY(tp_all_gather_f32(ws->logits_local, ws->logits, static_cast<long long>(B) * m->vocab, st));
-  } else if (!skip_lm) {
+  if (!skip_lm) {
+    // (tensor parallelism: m->vocab is this rank's shard; the logits stay sharded for the sampler)
     const bcg_gemm_fusion f = consumer(sumsq_mlp);
     BCG_TRY(gemm_bf16_tn_fused(ws->xn_last, m->lm_head, ws->logits, B, m->vocab, d, d, d, m->vocab,
-                               BCG_EPI_F32, 1, gf, (nf || dn) ? &f : nullptr, st));
+                               BCG_EPI_F32, 1, gf, scaled ? &f : nullptr, st));
   }
   return BCG_OK;
 }

@@ -79,7 +79,25 @@ __device__ __forceinline__ Best better(Best a, Best b) {
 
 struct SamplerDev {
   bcg_sampler_args a;
+  void* const* peers;   // symmetric buffers of the tensor-parallel replica (a.tp_size > 1), else null
 };
+
+// Vocab-parallel sampling (tensor parallelism): every rank scans only ITS shard of the vocabulary
+// and the ranks exchange one (score, token id) candidate per row instead of gathering [B, V] logits.
+// A candidate travels as two 8-byte words {score bits, epoch} {token id, epoch} written with single
+// 64-bit stores into every peer's symmetric buffer; the reader spins until both words carry the
+// row's current epoch (the per-row launch counter every rank keeps in lock step), so no separate
+// flag or fence is needed.  Two parity slots per (source rank, row).
+constexpr int kCandOffEpoch = 2 * 1024 + 2 * 8 * 1024;      // after tp_reduce_norm.cu's counters and flags
+constexpr int kCandOff = kCandOffEpoch + 128;               // [2][8][128][4] words
+__device__ __forceinline__ void st_sys_v2(int* p, int a, int b) {
+  asm volatile("st.relaxed.sys.global.v2.s32 [%0], {%1, %2};" ::"l"(p), "r"(a), "r"(b) : "memory");
+}
+__device__ __forceinline__ int2 ld_sys_v2(const int* p) {
+  int2 r;
+  asm volatile("ld.relaxed.sys.global.v2.s32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p) : "memory");
+  return r;
+}
 
 __global__ void __cluster_dims__(kSampCluster, 1, 1) __launch_bounds__(kSampThreads)
 mask_sample_kernel(const SamplerDev p) {
@@ -105,28 +123,30 @@ mask_sample_kernel(const SamplerDev p) {
     const uint32_t k0 = a.seed[2 * row], k1 = a.seed[2 * row + 1];
     const uint32_t step = static_cast<uint32_t>(a.n_out[row]);
     const float* lg = a.logits + static_cast<long long>(row) * (a.shard_v > 0 ? a.shard_v : a.ld_logits);
-    // slice in units of 128 elements so float4 chunks and 32-bit mask words never straddle
+    // slice in units of 128 elements so float4 chunks never straddle; a group of 4 tokens starts at
+    // a multiple of 4 of the GLOBAL id (vocab_base % 4 == 0), so its mask bits sit in one word
     const int per = ((a.V + kSampCluster * 128 - 1) / (kSampCluster * 128)) * 128;
     const int i0 = static_cast<int>(rank) * per;
     const int i1 = min(a.V, i0 + per);
     for (int i = i0 + 4 * threadIdx.x; i < i1; i += 4 * kSampThreads) {
       const float4 x = *reinterpret_cast<const float4*>(
           a.shard_v > 0 ? lg + static_cast<long long>(i / a.shard_v) * a.shard_stride + i % a.shard_v : lg + i);
+      const int gi = a.vocab_base + i;   // token id (this rank's shard starts at vocab_base)
       uint32_t bits = 0xFu;
-      if (mask) bits = (static_cast<uint32_t>(mask[i >> 5]) >> (i & 31)) & 0xFu;
+      if (mask) bits = (static_cast<uint32_t>(mask[gi >> 5]) >> (gi & 31)) & 0xFu;
       if (bits == 0) continue;
       float s0 = x.x, s1 = x.y, s2 = x.z, s3 = x.w;
       if (!greedy) {
-        const uint4 r = philox4x32_10(static_cast<uint32_t>(i >> 2), step, 0u, 0u, k0, k1);
+        const uint4 r = philox4x32_10(static_cast<uint32_t>(gi >> 2), step, 0u, 0u, k0, k1);
         s0 = race_score(x.x, temp, r.x);
         s1 = race_score(x.y, temp, r.y);
         s2 = race_score(x.z, temp, r.z);
         s3 = race_score(x.w, temp, r.w);
       }
-      if (bits & 1u) best = better(best, Best{s0, i});
-      if (bits & 2u) best = better(best, Best{s1, i + 1});
-      if (bits & 4u) best = better(best, Best{s2, i + 2});
-      if (bits & 8u) best = better(best, Best{s3, i + 3});
+      if (bits & 1u) best = better(best, Best{s0, gi});
+      if (bits & 2u) best = better(best, Best{s1, gi + 1});
+      if (bits & 4u) best = better(best, Best{s2, gi + 2});
+      if (bits & 8u) best = better(best, Best{s3, gi + 3});
     }
   }
 #pragma unroll
@@ -150,6 +170,32 @@ mask_sample_kernel(const SamplerDev p) {
   if (rank == 0 && threadIdx.x == 0 && !row_done) {
     Best b = cta_best[0];
     for (int r = 1; r < kSampCluster; ++r) b = better(b, cta_best[r]);
+    if (a.tp_size > 1) {
+      // b is the best of this rank's vocabulary shard: trade it for every peer's and keep the winner
+      // (same total order on every rank: higher score, then lower token id)
+      int* local = reinterpret_cast<int*>(p.peers[a.tp_rank]);
+      const int ep = local[kCandOffEpoch + row] + 1;
+      local[kCandOffEpoch + row] = ep;
+      const int par = ep & 1;
+      for (int pr = 0; pr < a.tp_size; ++pr) {
+        if (pr == a.tp_rank) continue;
+        int* dst = reinterpret_cast<int*>(p.peers[pr]) + kCandOff + ((par * 8 + a.tp_rank) * 128 + row) * 4;
+        st_sys_v2(dst, __float_as_int(b.s), ep);
+        st_sys_v2(dst + 2, b.i, ep);
+      }
+      for (int src = 0; src < a.tp_size; ++src) {
+        if (src == a.tp_rank) continue;
+        const int* in = local + kCandOff + ((par * 8 + src) * 128 + row) * 4;
+        int2 w0, w1;
+        unsigned spins = 0;
+        do {
+          w0 = ld_sys_v2(in);
+          w1 = ld_sys_v2(in + 2);
+          if (++spins > (1u << 24)) __trap();   // a peer died: fail loudly instead of hanging
+        } while (w0.y != ep || w1.y != ep);
+        b = better(b, Best{__int_as_float(w0.x), w1.x});
+      }
+    }
     const int step = a.n_out[row];
     int fin = 0;
     int chosen = b.i;
@@ -217,12 +263,23 @@ int mask_sample(const bcg_sampler_args* a, cudaStream_t stream) {
       !a->grammar_id || !a->temperature || !a->seed || !a->max_tokens || !a->state || !a->n_out ||
       !a->finished || !a->out_tokens || !a->next_ids || !a->positions || !a->seq_lens ||
       !a->slot_map || !a->block_table || !a->tok_offsets || !a->tok_bytes || a->page_size <= 0 ||
-      a->mask_words < (a->V + 31) / 32 || (a->shard_v > 0 && (a->shard_v % 4))) {
-    set_last_error("bcg_mask_sample", "bad argument (null pointer, V % 4, or mask_words too small)");
+      a->mask_words < (a->vocab_base + a->V + 31) / 32 || (a->shard_v > 0 && (a->shard_v % 4)) ||
+      a->vocab_base < 0 || (a->vocab_base % 4)) {
+    set_last_error("bcg_mask_sample", "bad argument (null pointer, V % 4, vocab_base % 4, or mask_words too small)");
     return BCG_ERR_ARG;
   }
   SamplerDev p;
   p.a = *a;
+  p.peers = nullptr;
+  if (a->tp_size > 1) {
+    if (a->tp_size > 8 || a->tp_rank < 0 || a->tp_rank >= a->tp_size || a->B > 128 || !tp_symm_peers_device() ||
+        tp_size() != a->tp_size) {
+      set_last_error("bcg_mask_sample", "vocab-parallel sampling needs bcg_tp_init + the symmetric buffer, "
+                                        "tp_size <= 8 and at most 128 rows");
+      return BCG_ERR_ARG;
+    }
+    p.peers = tp_symm_peers_device();
+  }
   BCG_CUDA_CHECK(launch_k(mask_sample_kernel, dim3(kSampCluster, a->B), dim3(kSampThreads), 0, stream, p));
   if (a->n_active) {
     BCG_CUDA_CHECK(launch_k(count_active_kernel, dim3(1), dim3(32), 0, stream,

@@ -1,33 +1,46 @@
-// Fused tensor-parallel all-reduce + residual add + RMSNorm for the decode step, over NVLink /
-// NVSwitch peer memory — no NCCL call, no separate reduction kernel.
+// Fused tensor-parallel all-reduce + residual add + RMSNorm statistics for the decode step, over
+// NVLink / NVSwitch peer memory — no NCCL call, no separate reduction or signalling kernel.
 //
 // After a row-parallel projection (o_proj, down_proj) every rank holds split-K partial slabs of
-// ITS share of the sum.  Those slabs live in a symmetric buffer that all ranks of the replica
-// have mapped (cudaIpc).  Each rank then
-//   1. tp_signal_kernel: bumps its epoch for the slot and stores it, with release semantics at
-//      system scope, into every peer's flag array (a kernel boundary after the GEMM guarantees
-//      the slabs are complete);
-//   2. tp_add_rmsnorm_kernel: waits (acquire, bounded spin) until every peer's flag has reached
-//      the epoch, reads ALL ranks' slabs straight from peer memory with L1-bypassing loads, adds
-//      them in a fixed (rank, split) order — so every rank computes bit-identical sums — adds the
-//      residual and normalises.
-// A 10-row all-reduce is ~200 KB per rank: the cost is a flag round trip over NVLink plus a
-// few microseconds of peer reads, instead of ~35-55 us of NCCL latency, 2 x n_layers times a step.
-// Two slots (o / down) alternate, which is enough to make buffer reuse safe: a rank overwrites
-// slot s only after the NEXT wait on the other slot, which every peer signals only after it has
-// finished reading slot s.
+// ITS share of the sum in its LOCAL scratch.  One kernel per all-reduce, grid (8 segments, rows),
+// the same decomposition on every rank; CTA (segment, row) of rank r
+//   1. adds its local slabs in index order  ->  one fp32 partial per element (B*d floats per rank,
+//      not splits*B*d: the exchange carries the reduced message only);
+//   2. PUSHES that partial into slot [r] of every peer's symmetric buffer with plain stores over
+//      NVLink (posted writes: one-way latency), then — barrier, system fence — releases an epoch flag
+//      [r][cta] on every peer;
+//   3. waits (acquire, bounded spin) for the flags [src][cta] of all peers on its OWN buffer and
+//      adds the size partials in rank order (its own from registers): every rank forms the same
+//      sum bit for bit;
+//   4. finishes like bcg_add_norm_stats: residual += sum, xn = bf16(residual * w), the segment's
+//      sum of squares to sumsq[segment][row]; the projection that reads xn applies 1/RMS in its
+//      epilogue (bcg_gemm_bf16_tn_fused consumer half).
+// A CTA only ever waits for the CTA with its own index on other GPUs, so nothing needs to be
+// co-resident and the kernel composes with programmatic dependent launch.  Per all-reduce a rank
+// sends (size-1) * B*d*4 bytes (1.4 MB at 10 rows, d 5120, TP 8) and receives as much; reads after
+// the wait are local.  Two slots (o / down) alternate, which makes buffer reuse safe: a rank
+// overwrites slot s only two all-reduces later, and it cannot finish the one in between before
+// every peer has released its flag there — which a peer does only after its kernel on slot s ended.
 //
-// Symmetric buffer layout (floats): [flag area: kFlagFloats][slot 0 slabs][slot 1 slabs]
+// Symmetric buffer layout (4-byte words): header kTpHeaderWords, then [slot 2][src size][region].
+//   header: launch counters [2][1024] (local), flags [2][8][1024], sampler epochs [128] (local),
+//           sampler candidates [2][8][128][4]  (see sampler.cu)
 #include "common.cuh"
 #include "kernels.h"
 
 namespace bcg {
 
 constexpr int kTpMax = 8;
-constexpr long long kFlagFloats = 256;     // epochs[2] at 0..1, flags[2][8] at 64.. (ints)
-constexpr int kTpNormThreads = 1024;
+constexpr int kTpMaxCtas = 1024;                       // 128 rows x 8 segments
+constexpr long long kTpHeaderWords = 32768;
+constexpr int kTpOffEpoch = 0;                         // [2][kTpMaxCtas]
+constexpr int kTpOffFlags = 2 * kTpMaxCtas;            // [2][kTpMax][kTpMaxCtas]
+constexpr int kTpSegments = 8;
+constexpr int kTpSegThreads = 256;
+constexpr int kTpSegTurns = 2;                         // d <= 8 * 256 * 2 * 4 = 16384
+constexpr int kTpStatsStride = 128;
 
-long long tp_symm_flag_floats() { return kFlagFloats; }
+long long tp_symm_flag_floats() { return kTpHeaderWords; }
 
 __device__ __forceinline__ void st_release_sys(int* p, int v) {
   asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -37,7 +50,7 @@ __device__ __forceinline__ int ld_acquire_sys(const int* p) {
   asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-__device__ __forceinline__ float4 ld_peer_v4(const float* p) {
+__device__ __forceinline__ float4 ld_sys_v4(const float* p) {
   float4 r;
   asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];"
                : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
@@ -45,120 +58,141 @@ __device__ __forceinline__ float4 ld_peer_v4(const float* p) {
                : "memory");
   return r;
 }
-
-__global__ void tp_signal_kernel(void* const* __restrict__ peers, int rank, int size, int slot) {
-  pdl_launch_dependents();
-  pdl_wait();
-  int* local = reinterpret_cast<int*>(peers[rank]);
-  __shared__ int epoch;
-  if (threadIdx.x == 0) {
-    epoch = local[slot] + 1;
-    local[slot] = epoch;
-    __threadfence_system();
-  }
-  __syncthreads();
-  if (threadIdx.x < size) {
-    int* flags = reinterpret_cast<int*>(peers[threadIdx.x]) + 64 + slot * kTpMax + rank;
-    st_release_sys(flags, epoch);
-  }
+__device__ __forceinline__ void st_sys_v4(float* p, const float4& v) {
+  asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
 }
 
-__global__ void __launch_bounds__(kTpNormThreads)
-tp_add_rmsnorm_kernel(float* __restrict__ residual, void* const* __restrict__ peers, int rank, int size,
-                      long long region_offset, int n_partials, long long partial_stride,
-                      const float* __restrict__ w, __nv_bfloat16* __restrict__ xn, int slot, int d,
-                      float eps) {
-  __shared__ float red[kTpNormThreads / 32];
+__global__ void __launch_bounds__(kTpSegThreads)
+tp_add_norm_stats_kernel(float* __restrict__ residual, const float* __restrict__ partials, int n_partials,
+                         long long partial_stride, const float* __restrict__ w,
+                         __nv_bfloat16* __restrict__ xn, float* __restrict__ sumsq, int d,
+                         void* const* __restrict__ peers, int rank, int size, int slot, long long region) {
+  __shared__ float red[kTpSegThreads / 32];
+  __shared__ int s_epoch;
   pdl_launch_dependents();
+  const int seg = blockIdx.x, t = blockIdx.y;
+  const int cta = t * kTpSegments + seg;
+  int* local = reinterpret_cast<int*>(peers[rank]);
+  const int nvec = d >> 2;
+  const int per = (nvec + kTpSegments - 1) / kTpSegments;
+  const int v_end = min(nvec, (seg + 1) * per);
   pdl_wait();
-  const int* local = reinterpret_cast<const int*>(peers[rank]);
-  if (threadIdx.x < size) {
-    const int want = local[slot];   // written by this rank's tp_signal_kernel, earlier on this stream
-    const int* flag = local + 64 + slot * kTpMax + threadIdx.x;
+  if (threadIdx.x == 0) {
+    const int e = local[kTpOffEpoch + slot * kTpMaxCtas + cta] + 1;
+    local[kTpOffEpoch + slot * kTpMaxCtas + cta] = e;
+    s_epoch = e;
+  }
+  // 1. local split-K slabs -> one partial per element; 2. push it to every peer
+  float4 mine[kTpSegTurns];
+  bool have[kTpSegTurns];
+  const long long slot_base = kTpHeaderWords + static_cast<long long>(slot) * size * region;
+#pragma unroll
+  for (int i = 0; i < kTpSegTurns; ++i) {
+    const int v = seg * per + threadIdx.x + i * kTpSegThreads;
+    have[i] = threadIdx.x + i * kTpSegThreads < per && v < v_end;
+    mine[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (have[i]) {
+      const long long off = static_cast<long long>(t) * d + v * 4;
+      const float* dp = partials + off;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int s0 = 0; s0 < n_partials; s0 += 8) {
+        float4 p[8];
+#pragma unroll
+        for (int s = 0; s < 8; ++s)   // unconditional, clamped: all eight loads in flight at once
+          p[s] = *reinterpret_cast<const float4*>(dp + min(s0 + s, n_partials - 1) * partial_stride);
+#pragma unroll
+        for (int s = 0; s < 8; ++s) {
+          if (s0 + s < n_partials) {
+            if (s0 + s == 0) {
+              acc = p[s];
+            } else {
+              acc.x += p[s].x; acc.y += p[s].y; acc.z += p[s].z; acc.w += p[s].w;
+            }
+          }
+        }
+      }
+      mine[i] = acc;
+      for (int pr = 0; pr < size; ++pr) {
+        if (pr == rank) continue;
+        st_sys_v4(reinterpret_cast<float*>(peers[pr]) + slot_base + rank * region + off, acc);
+      }
+    }
+  }
+  __syncthreads();   // every thread's pushes are issued; s_epoch is visible
+  const int epoch = s_epoch;
+  if (threadIdx.x < size && threadIdx.x != rank) {
+    __threadfence_system();
+    st_release_sys(reinterpret_cast<int*>(peers[threadIdx.x]) + kTpOffFlags +
+                       (slot * kTpMax + rank) * kTpMaxCtas + cta, epoch);
+    // 3. wait for that peer's partial of this (row, segment)
+    const int* flag = local + kTpOffFlags + (slot * kTpMax + threadIdx.x) * kTpMaxCtas + cta;
     unsigned spins = 0;
-    while (ld_acquire_sys(flag) < want) {
+    while (ld_acquire_sys(flag) < epoch) {
       if (++spins > (1u << 24)) __trap();   // a peer died: fail loudly instead of hanging the GPU
     }
   }
   __syncthreads();
-  const int t = blockIdx.x;
-  const int nvec = d >> 2;
-  float4 x[2];
+  const float* inbox = reinterpret_cast<const float*>(local) + slot_base;
   float ss = 0.f;
 #pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    const int v = threadIdx.x + i * kTpNormThreads;
-    if (v < nvec) {
-      float4 r = *reinterpret_cast<const float4*>(residual + static_cast<long long>(t) * d + v * 4);
-      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-      // all (rank, split) slabs as one flat list, loaded eight at a time so that a whole batch
-      // of peer reads shares one NVLink round trip; summed in list order = fixed (rank, split)
-      // order on every rank
-      const int total = size * n_partials;
-      const long long elem = static_cast<long long>(t) * d + v * 4;
-      for (int i0 = 0; i0 < total; i0 += 8) {
-        float4 p[8];
+  for (int i = 0; i < kTpSegTurns; ++i) {
+    if (have[i]) {
+      const int v = seg * per + threadIdx.x + i * kTpSegThreads;
+      const long long off = static_cast<long long>(t) * d + v * 4;
+      float4 p[kTpMax];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const int idx = i0 + k;
-          if (idx < total) {
-            const int rk = idx / n_partials, sp = idx - rk * n_partials;
-            p[k] = ld_peer_v4(reinterpret_cast<const float*>(peers[rk]) + region_offset + elem +
-                              sp * partial_stride);
+      for (int src = 0; src < kTpMax; ++src)   // clamped: all peer slots requested before any add
+        p[src] = ld_sys_v4(inbox + min(src, size - 1) * region + off);
+      float4 tot = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int src = 0; src < kTpMax; ++src) {
+        if (src < size) {
+          const float4 a = (src == rank) ? mine[i] : p[src];
+          if (src == 0) {
+            tot = a;
+          } else {
+            tot.x += a.x; tot.y += a.y; tot.z += a.z; tot.w += a.w;
           }
         }
-#pragma unroll
-        for (int k = 0; k < 8; ++k)
-          if (i0 + k < total) {
-            acc.x += p[k].x; acc.y += p[k].y; acc.z += p[k].z; acc.w += p[k].w;
-          }
       }
-      r.x += acc.x; r.y += acc.y; r.z += acc.z; r.w += acc.w;
-      x[i] = r;
-      ss += r.x * r.x + r.y * r.y + r.z * r.z + r.w * r.w;
+      float4 x = *reinterpret_cast<const float4*>(residual + off);
+      x.x += tot.x; x.y += tot.y; x.z += tot.z; x.w += tot.w;
+      const float4 ww = *reinterpret_cast<const float4*>(w + v * 4);
+      ss = __fadd_rn(ss, __fmaf_rn(x.w, x.w, __fmaf_rn(x.z, x.z, __fmaf_rn(x.y, x.y, __fmul_rn(x.x, x.x)))));
+      *reinterpret_cast<float4*>(residual + off) = x;
+      uint2 o;
+      o.x = pack_bf16(x.x * ww.x, x.y * ww.y);
+      o.y = pack_bf16(x.z * ww.z, x.w * ww.w);
+      *reinterpret_cast<uint2*>(xn + off) = o;
     }
   }
   ss = warp_sum(ss);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (lane == 0) red[warp] = ss;
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
   __syncthreads();
-  float tot = 0.f;
+  if (threadIdx.x == 0) {
+    float sg = 0.f;
 #pragma unroll
-  for (int i = 0; i < kTpNormThreads / 32; ++i) tot += red[i];
-  const float inv = rsqrtf(tot / static_cast<float>(d) + eps);
-#pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    const int v = threadIdx.x + i * kTpNormThreads;
-    if (v < nvec) {
-      *reinterpret_cast<float4*>(residual + static_cast<long long>(t) * d + v * 4) = x[i];
-      const float4 ww = *reinterpret_cast<const float4*>(w + v * 4);
-      uint2 o;
-      o.x = pack_bf16(x[i].x * inv * ww.x, x[i].y * inv * ww.y);
-      o.y = pack_bf16(x[i].z * inv * ww.z, x[i].w * inv * ww.w);
-      *reinterpret_cast<uint2*>(xn + static_cast<long long>(t) * d + v * 4) = o;
-    }
+    for (int i = 0; i < kTpSegThreads / 32; ++i) sg += red[i];
+    sumsq[seg * kTpStatsStride + t] = sg;
   }
 }
 
-int tp_signal(int slot, cudaStream_t stream) {
-  if (!tp_symm_peers_device()) {
-    set_last_error("bcg_tp", "symmetric buffer not set up");
+int tp_add_norm_stats(float* residual, const float* partials, int n_partials, long long partial_stride,
+                      const float* w, void* xn, float* sumsq, int slot, long long region_floats, int T,
+                      int d, cudaStream_t stream) {
+  if (!tp_symm_peers_device() || !residual || !partials || !w || !xn || !sumsq || T <= 0 || T > 128 ||
+      (d % 4) || d > kTpSegments * kTpSegThreads * kTpSegTurns * 4 || n_partials < 1 || slot < 0 || slot > 1 ||
+      static_cast<long long>(T) * d > region_floats || tp_size() > kTpMax ||
+      (kTpHeaderWords + 2 * tp_size() * region_floats) * 4 > tp_symm_bytes()) {
+    set_last_error("bcg_tp_add_norm_stats", "bad argument, more than 128 rows, or symmetric buffer too small / not set up");
     return BCG_ERR_ARG;
   }
-  BCG_CUDA_CHECK(launch_k(tp_signal_kernel, dim3(1), dim3(32), 0, stream, tp_symm_peers_device(), tp_rank(),
-                          tp_size(), slot));
-  return BCG_OK;
-}
-
-int tp_add_rmsnorm(float* residual, long long region_offset_floats, int n_partials, long long partial_stride,
-                   const float* w, void* xn, int slot, int T, int d, float eps, cudaStream_t stream) {
-  if (!tp_symm_peers_device() || !residual || !w || !xn || T <= 0 || (d % 4) || d > kTpNormThreads * 8) {
-    set_last_error("bcg_tp_add_rmsnorm", "bad argument or symmetric buffer not set up");
-    return BCG_ERR_ARG;
-  }
-  BCG_CUDA_CHECK(launch_k(tp_add_rmsnorm_kernel, dim3(T), dim3(kTpNormThreads), 0, stream, residual,
-                          tp_symm_peers_device(), tp_rank(), tp_size(), region_offset_floats, n_partials,
-                          partial_stride, w, reinterpret_cast<__nv_bfloat16*>(xn), slot, d, eps));
+  BCG_CUDA_CHECK(launch_k(tp_add_norm_stats_kernel, dim3(kTpSegments, T), dim3(kTpSegThreads), 0, stream,
+                          residual, partials, n_partials, partial_stride, w,
+                          reinterpret_cast<__nv_bfloat16*>(xn), sumsq, d, tp_symm_peers_device(), tp_rank(),
+                          tp_size(), slot, region_floats));
   return BCG_OK;
 }
 

@@ -39,6 +39,8 @@ PAGE = 16
 SPLIT_TOKENS = 256
 MAX_GRAMMARS = 64
 POLL_EVERY = 16
+# query rows per prefill-attention CTA (bcg_prefill_attn_paged)
+PREFILL_TILE = 64 if __import__("os").environ.get("BCG_PREFILL_ATTN_LEGACY") else 128
 
 
 def row_seed(base_seed: int, call_index: int, row: int):
@@ -172,7 +174,9 @@ class Engine:
         self.use_cuda_graph = use_cuda_graph
         # How decode runs the residual add + RMSNorm between projections (include/bcg_b200.h,
         # bcg_model_decode).  Default on one GPU: statistics kernel + 1/RMS in the next GEMM's epilogue
-        # (1.5 % faster per step than the complete norm kernel); TP engines keep the reduce+norm kernels.
+        # (1.5 % faster per step than the complete norm kernel).  TP engines with the fused all-reduce
+        # do the same inside bcg_tp_add_norm_stats; with NCCL all-reduces they run the complete norm.
+        self.tp_group = tp_group
         if deferred_norm is None:
             deferred_norm = tp_size == 1 and not fused_norm
         self.flags = ((L.GEMM_PDL if pdl else 0) | (L.STEP_FUSED_NORM if fused_norm else 0)
@@ -198,10 +202,8 @@ class Engine:
             sml=z(B * lc.n_heads * self.max_splits_cap * 2, dt=f32),
             attn_counters=z(B * lc.n_kv_heads, dt=i32),
             row_sumsq=z(2 * max((d + 127) // 128, 8) * 128, dt=f32), tile_counters=z((d + 127) // 128, dt=i32),
-            logits=z(B, full_cfg.vocab, dt=f32), xn_last=z(B, d))
-        if tp_size > 1:
-            self.buf["logits_local"] = z(B, lc.vocab, dt=f32)
-            self.buf["logits_group"] = z(B, full_cfg.vocab, dt=f32)
+            # under tensor parallelism the logits stay sharded: [B, vocab / tp] per rank
+            logits=z(B, lc.vocab, dt=f32), xn_last=z(B, d))
         ws = L.Workspace()
         b = self.buf
         ws.residual, ws.xn, ws.qkv, ws.q = b["residual"].data_ptr(), b["xn"].data_ptr(), b["qkv"].data_ptr(), b["q"].data_ptr()
@@ -211,17 +213,17 @@ class Engine:
         ws.attn_counters = b["attn_counters"].data_ptr()
         ws.max_splits = self.max_splits_cap
         ws.logits, ws.xn_last, ws.T_max, ws.B_max = b["logits"].data_ptr(), b["xn_last"].data_ptr(), T, B
-        ws.logits_local = b["logits_local"].data_ptr() if tp_size > 1 else None
-        # tables for the opt-in norm fusion (fused_norm=True; single-GPU engines, d_model % 128 == 0)
-        fuse_norm = tp_size == 1 and d % 128 == 0
-        ws.row_sumsq = b["row_sumsq"].data_ptr() if fuse_norm else None
-        ws.tile_counters = b["tile_counters"].data_ptr() if fuse_norm else None
+        ws.logits_local = None
+        # tables for the deferred / fused norm (row sums of squares; tile counters for fused_norm=True)
+        ws.row_sumsq = b["row_sumsq"].data_ptr()
+        ws.tile_counters = b["tile_counters"].data_ptr() if (tp_size == 1 and d % 128 == 0) else None
         ws.tp_region_floats = 0
-        if tp_size > 1 and tp_fused_allreduce:
-            # decode all-reduces fused into the norm kernels over NVLink peer memory
+        if tp_size > 1:
+            # The symmetric buffer (cudaIpc over NVLink) carries the sampler's candidate exchange
+            # and, with tp_fused_allreduce, the decode step's all-reduces (bcg_tp_add_norm_stats).
             from . import tp as _tp
-            region = max(splits[1], splits[3]) * B * d
-            _tp.setup_symmetric(4 * (256 + 2 * region), tp_rank, tp_size, tp_group)
+            region = B * d if tp_fused_allreduce else 0
+            _tp.setup_symmetric(int(self.lib.bcg_tp_symm_bytes_for(region, tp_size)), tp_rank, tp_size, tp_group)
             ws.tp_region_floats = region
         self.ws = ws
         # ---- KV pages
@@ -231,6 +233,13 @@ class Engine:
             budget = int(total_b * gpu_memory_utilization) - (total_b - free_b)
             want = self.max_rows * self.max_blocks * 2
             kv_pages = max(self.max_blocks + 8, min(want, budget // page_bytes))
+            if tp_size > 1:
+                # every rank must run the SAME page pool (eviction, cache hits and prefill sizes are
+                # decided per rank and have to agree): take the smallest budget of the replica
+                import torch.distributed as dist
+                t = torch.tensor([kv_pages], dtype=torch.int64)
+                dist.all_reduce(t, op=dist.ReduceOp.MIN, group=tp_group)
+                kv_pages = int(t.item())
         self.kv_layers = [z(kv_pages, 2, lc.n_kv_heads, PAGE, 128) for _ in range(cfg.n_layers)]
         self.pool = PagePool(kv_pages)
         self.model = ModelHandle(weights, self.kv_layers, PAGE, tp_size)
@@ -289,8 +298,8 @@ class Engine:
     # ------------------------------------------------------------------ sampler / steps
     def _sampler_args(self, B: int, use_forced: bool) -> L.SamplerArgs:
         r, a = self.row, L.SamplerArgs()
-        a.logits, a.ld_logits = self.buf["logits"].data_ptr(), self.cfg.vocab
-        a.B, a.V, a.mask_words, a.max_steps = B, self.cfg.vocab, self.mask_words, self.max_steps
+        a.logits, a.ld_logits = self.buf["logits"].data_ptr(), self.lcfg.vocab
+        a.B, a.V, a.mask_words, a.max_steps = B, self.lcfg.vocab, self.mask_words, self.max_steps
         stops = list(self.tk.stop_ids) + [-1]
         a.eos_id0, a.eos_id1 = stops[0], stops[1]
         a.page_size, a.max_blocks_per_seq = PAGE, self.max_blocks
@@ -304,8 +313,8 @@ class Engine:
         a.next_ids, a.positions = r["next_ids"].data_ptr(), r["positions"].data_ptr()
         a.seq_lens, a.slot_map = r["seq_lens"].data_ptr(), r["slot_map"].data_ptr()
         a.block_table, a.n_active = r["block_table"].data_ptr(), r["n_active"].data_ptr()
-        if self.tp_size > 1:   # logits as the all-gather left them: [tp][B][V/tp]
-            a.shard_v, a.shard_stride = self.lcfg.vocab, B * self.lcfg.vocab
+        if self.tp_size > 1:   # vocab-parallel sampling: local shard + one candidate per row exchanged
+            a.tp_rank, a.tp_size, a.vocab_base = self.tp_rank, self.tp_size, self.tp_rank * self.lcfg.vocab
         return a
 
     def _sample(self, B: int, use_forced: bool) -> None:
@@ -517,11 +526,15 @@ class Engine:
         return results
 
     def _logits_rows(self, B: int) -> torch.Tensor:
-        """[B, V] logits of the current step (un-shards the all-gather layout under TP)."""
+        """[B, V] logits of the current step (parity tests only; under TP the vocabulary shards are
+        gathered over the control group — the product path never moves logits between ranks)."""
         if self.tp_size == 1:
             return self.buf["logits"][:B].clone()
-        P, vp = self.tp_size, self.lcfg.vocab
-        return self.buf["logits"].view(-1)[:P * B * vp].view(P, B, vp).permute(1, 0, 2).reshape(B, P * vp).clone()
+        import torch.distributed as dist
+        mine = self.buf["logits"][:B].cpu()
+        parts = [torch.empty_like(mine) for _ in range(self.tp_size)]
+        dist.all_gather(parts, mine, group=self.tp_group)
+        return torch.cat(parts, dim=1).to(self.dev)
 
     def _prefill_group(self, b0, b1, ids_list, cached, bt) -> None:
         cfg, dev = self.cfg, self.dev
@@ -533,8 +546,8 @@ class Engine:
             p = np.arange(c, c + n)
             pos.append(p)
             slots.append(bt[b, p // PAGE] * PAGE + p % PAGE)
-            for q0 in range(0, n, 64):
-                tiles.append((b - b0, row + q0, c + q0, min(64, n - q0)))
+            for q0 in range(0, n, PREFILL_TILE):
+                tiles.append((b - b0, row + q0, c + q0, min(PREFILL_TILE, n - q0)))
             row += n
             last.append(row - 1)
         T, n_seqs = row, b1 - b0
@@ -544,11 +557,7 @@ class Engine:
         self.stats["h2d_bytes"] += sum(x.numel() * 4 for x in (d_ids, d_pos, d_slots, d_tiles, d_last, d_bt))
         # this group's last-token logits go straight to rows b0..b1 of the row-indexed buffer
         base = self.buf["logits"].data_ptr()
-        B_all = len(ids_list)
-        if self.tp_size > 1:
-            self.ws.logits = self.buf["logits_group"].data_ptr()   # gathered [tp][n_seqs][V/tp]
-        else:
-            self.ws.logits = base + b0 * cfg.vocab * 4
+        self.ws.logits = base + b0 * self.lcfg.vocab * 4
         try:
             L.check(self.lib.bcg_model_prefill(C.byref(self.model.struct), C.byref(self.ws),
                                                d_ids.data_ptr(), d_pos.data_ptr(), d_slots.data_ptr(),
@@ -557,10 +566,6 @@ class Engine:
                     "bcg_model_prefill")
         finally:
             self.ws.logits = base
-        if self.tp_size > 1:   # place the group's rows into the call-wide [tp][B][V/tp] layout
-            P, vp = self.tp_size, self.lcfg.vocab
-            dst = self.buf["logits"].view(-1)[:P * B_all * vp].view(P, B_all, vp)
-            dst[:, b0:b1] = self.buf["logits_group"].view(-1)[:P * n_seqs * vp].view(P, n_seqs, vp)
         self.stats["gpu_launches"] += cfg.n_layers * 8 + 2
         self._keepalive = (d_ids, d_pos, d_slots, d_tiles, d_last, d_bt)
 

@@ -40,6 +40,7 @@ class SamplerArgs(C.Structure):
         ("next_ids", vp), ("positions", vp), ("seq_lens", vp), ("slot_map", vp),
         ("block_table", vp), ("n_active", vp),
         ("shard_v", C.c_int), ("shard_stride", C.c_longlong),
+        ("tp_rank", C.c_int), ("tp_size", C.c_int), ("vocab_base", C.c_int),
     ]
 
 
@@ -100,13 +101,16 @@ _SIGS = {
                                             C.c_int, C.c_int, C.c_float, vp]),
     "bcg_decode_attn_paged_static": (C.c_int, [vp, vp, vp, C.c_int, vp, vp, C.c_int, C.c_int, C.c_int,
                                                C.c_int, C.c_int, C.c_float, vp]),
-    "bcg_prefill_attn_paged": (C.c_int, [vp, vp, vp, C.c_int, vp, C.c_int, vp, C.c_int, C.c_int,
+    "bcg_prefill_attn_paged": (C.c_int, [vp, vp, vp, C.c_int, vp, C.c_int, vp, C.c_int, C.c_int, C.c_int,
                                          C.c_int, C.c_float, vp]),
     "bcg_mask_sample": (C.c_int, [C.POINTER(SamplerArgs), vp]),
     "bcg_tp_unique_id": (C.c_int, [vp]),
     "bcg_tp_init": (C.c_int, [vp, C.c_int, C.c_int]),
     "bcg_tp_shutdown": (C.c_int, []),
+    "bcg_tp_symm_bytes_for": (C.c_longlong, [C.c_longlong, C.c_int]),
     "bcg_tp_symm_create": (C.c_int, [C.c_longlong, vp]),
+    "bcg_tp_add_norm_stats": (C.c_int, [vp, vp, C.c_int, C.c_longlong, vp, vp, vp, C.c_int, C.c_longlong,
+                                        C.c_int, C.c_int, vp]),
     "bcg_tp_symm_open": (C.c_int, [vp, C.c_int, C.c_int]),
     "bcg_model_prefill": (C.c_int, [C.POINTER(Model), C.POINTER(Workspace), vp, vp, vp, vp, C.c_int,
                                     vp, C.c_int, vp, C.c_int, C.c_int, vp]),

@@ -55,13 +55,48 @@ def broadcast_requests(reqs, group=None, src: int = 0):
     return box[0]
 
 
+def _gather_errors(err: Optional[str], group=None) -> List[Optional[str]]:
+    size = dist.get_world_size(group)
+    box: List[Optional[str]] = [None] * size
+    dist.all_gather_object(box, err, group=group)
+    return box
+
+
+def _describe(e: BaseException) -> str:
+    return f"{type(e).__name__}: {e}"
+
+
 def worker_loop(engine, group=None, src: int = 0) -> None:
-    """Ranks 1..tp-1 of a replica: run every generate() the leader runs, in lock step."""
+    """Ranks 1..tp-1 of a replica: run every generate() the leader runs, in lock step.  A call that
+    raises on this rank (page pool exhausted, oversized request: raised before any collective, and
+    on every rank alike since the ranks share pool size and requests) is reported to the leader
+    instead of killing the rank, so the replica stays usable."""
     while True:
         reqs = broadcast_requests(None, group, src)
         if isinstance(reqs, str) and reqs == STOP:
             return
-        engine.generate(reqs)
+        err = None
+        try:
+            engine.generate(reqs)
+        except Exception as e:  # noqa: BLE001 - reported to the leader below
+            err = _describe(e)
+        _gather_errors(err, group)
+
+
+def leader_generate(engine, reqs, group=None, src: int = 0):
+    """The leader's half of worker_loop: ship the requests, run them, then learn whether any rank
+    failed; a failure anywhere is raised here (the adapter turns it into its error dicts)."""
+    broadcast_requests(reqs, group, src)
+    err, out = None, None
+    try:
+        out = engine.generate(reqs)
+    except Exception as e:  # noqa: BLE001
+        err = _describe(e)
+    errs = _gather_errors(err, group)
+    bad = [f"rank {r}: {e}" for r, e in enumerate(errs) if e]
+    if bad:
+        raise L.BcgError("tensor-parallel generate failed — " + "; ".join(bad))
+    return out
 
 
 # ---------------------------------------------------------------------------------------------
@@ -98,10 +133,11 @@ def _build_engine(model_name: str, model_config: dict, rank: int, size: int):
                  kv_pages=model_config.get("kv_pages"),
                  base_seed=int(model_config.get("seed", os.environ.get("BCG_B200_SEED", 0))),
                  device=str(device), use_cuda_graph=bool(model_config.get("use_cuda_graph", True)),
-                 pdl=bool(model_config.get("pdl", False)), tp_rank=rank, tp_size=size,
-                 # measured: the peer-memory reduce beats NCCL at TP=2 (8.65 vs 9.70 ms/step, Mistral-22B)
-                 # and loses to NCCL's in-switch reduction at TP=8 (13.4 vs 8.9 ms/step, Qwen3-32B)
-                 tp_fused_allreduce=bool(model_config.get("tp_fused_allreduce", size == 2)))
+                 pdl=bool(model_config.get("pdl", True)), tp_rank=rank, tp_size=size,
+                 # decode all-reduces inside bcg_tp_add_norm_stats (pushes over NVLink) unless asked
+                 # for NCCL
+                 tp_fused_allreduce=bool(model_config.get("tp_fused_allreduce", True)),
+                 tp_group=model_config.get("tp_group"))
     return cfg, tok, eng
 
 
@@ -156,8 +192,7 @@ class SpawnedTP:
         self.size = size
 
     def generate(self, reqs):
-        broadcast_requests(reqs)
-        return self.engine.generate(reqs)
+        return leader_generate(self.engine, reqs)
 
     def close(self):
         try:
@@ -172,3 +207,57 @@ class SpawnedTP:
                 p.join(timeout=30)
                 if p.is_alive():
                     p.terminate()
+
+
+# ---------------------------------------------------------------------------------------------
+# Replicas inside an existing torch.distributed job (torchrun): TP composes with data parallelism
+# ---------------------------------------------------------------------------------------------
+def replica_groups(tp_size: int):
+    """Collective over the WHOLE job: cut the world into consecutive replicas of tp_size ranks and
+    create one gloo control group per replica.  Returns (this rank's group, its position in the
+    replica, the replica index, the global rank of the replica's leader)."""
+    world, rank = dist.get_world_size(), dist.get_rank()
+    if world % tp_size:
+        raise L.BcgError(f"world size {world} is not a multiple of tensor_parallel_size {tp_size}")
+    mine = None
+    for r0 in range(0, world, tp_size):
+        g = dist.new_group(list(range(r0, r0 + tp_size)), backend="gloo")   # every rank creates every group
+        if r0 <= rank < r0 + tp_size:
+            mine = g
+    return mine, rank % tp_size, rank // tp_size, (rank // tp_size) * tp_size
+
+
+class GroupTP:
+    """Leader (position 0) of a replica whose other ranks are processes of the same torch.distributed
+    job running serve_worker().  `model_config` carries the replica: "tp_group" (from replica_groups),
+    "tp_leader" (global rank) and "device" = the leader's GPU; rank i of the replica uses the GPU
+    i ordinals above it."""
+
+    def __init__(self, model_name: str, model_config: dict, size: int):
+        self.group, self.src = model_config["tp_group"], int(model_config.get("tp_leader", dist.get_rank()))
+        torch.cuda.set_device(_device_for(model_config, 0))
+        init_comm(0, size, self.group, self.src)
+        self.cfg, self.tokenizer, self.engine = _build_engine(model_name, model_config, 0, size)
+        self.size = size
+
+    def generate(self, reqs):
+        return leader_generate(self.engine, reqs, self.group, self.src)
+
+    def close(self):
+        broadcast_requests(STOP, self.group, self.src)
+        self.engine.close()
+        torch.cuda.synchronize()
+        shutdown_comm()
+
+
+def serve_worker(model_name: str, model_config: dict, position: int, size: int) -> None:
+    """Positions 1..size-1 of a GroupTP replica: build this rank's shard and serve until the leader
+    closes.  Call it from the worker ranks where the leader constructs its VLLMAgent."""
+    group, src = model_config["tp_group"], int(model_config["tp_leader"])
+    torch.cuda.set_device(_device_for(model_config, position))
+    init_comm(position, size, group, src)
+    _, _, eng = _build_engine(model_name, model_config, position, size)
+    worker_loop(eng, group, src)
+    eng.close()
+    torch.cuda.synchronize()
+    shutdown_comm()

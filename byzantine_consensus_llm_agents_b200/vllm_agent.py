@@ -83,8 +83,10 @@ class B200LLM:
         if tp_size > 1:
             # the reference has vLLM spawn `mp` workers here (vllm_agent.py:141-142); same shape:
             # this process is rank 0, ranks 1..tp-1 are spawned, one per additional GPU
-            from .tp import SpawnedTP
-            self.tp = SpawnedTP(model_name, model_config, tp_size)
+            # (or, inside a torchrun job, the replica's other ranks already exist: model_config["tp_group"])
+            from .tp import GroupTP, SpawnedTP
+            cls = GroupTP if model_config.get("tp_group") is not None else SpawnedTP
+            self.tp = cls(model_name, model_config, tp_size)
             self.cfg, self.tokenizer, self.engine = self.tp.cfg, self.tp.tokenizer, self.tp.engine
             return
         key = model_name.lower()

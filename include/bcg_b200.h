@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define BCG_ABI_VERSION 1
+#define BCG_ABI_VERSION 2
 
 /* status codes */
 #define BCG_STATUS_OK 0
@@ -172,12 +172,17 @@ int bcg_decode_attn_paged_static(const void* q, const void* kv_cache, const int*
                                  float scale, void* stream);
 
 /* Causal attention of ragged new-token rows against cached prefix + new tokens, both read
- * through the block table.  tile_info: int32 [n_tiles][4] = {sequence, first q row, position
- * of that row in its sequence, rows (<= 64)}.
+ * through the block table.  q and out are bf16 [n_q_rows, n_heads*128]; tile_info: int32
+ * [n_tiles][4] = {sequence, first q row, position of that row in its sequence, rows (<= 128)}.
+ * Both contractions run on tcgen05 tensor cores (accumulators in TMEM); q tiles and KV pages are
+ * fetched by TMA through tensor maps over the caller's q buffer and KV cache.  Every KV page a tile
+ * reads (pages 0 .. ceil((position + rows) / 16) - 1 of its sequence's block-table row) must hold
+ * finite values, including the unwritten tail of the last page (zero-initialise the cache).
  * Stands in for the FlashInfer paged prefill kernel. */
 int bcg_prefill_attn_paged(const void* q, const void* kv_cache, const int* block_table,
                            int max_blocks_per_seq, const int* tile_info, int n_tiles, void* out,
-                           int n_heads, int n_kv_heads, int page_size, float scale, void* stream);
+                           int n_q_rows, int n_heads, int n_kv_heads, int page_size, float scale,
+                           void* stream);
 
 /* Grammar-constrained sampler + per-row decode bookkeeping, one thread-block cluster per row.
  * Applies the JSON-schema token bitmask of the row's DFA state, then greedy argmax
@@ -226,6 +231,14 @@ typedef struct bcg_sampler_args {
    * logits[(i / shard_v) * shard_stride + b * shard_v + i % shard_v]; 0 = plain [B, ld_logits] */
   int shard_v;
   long long shard_stride;
+  /* vocab-parallel sampling without moving logits (tensor parallelism): tp_size > 1
+   * means `logits` holds only this rank's shard — V tokens starting at token id vocab_base (a
+   * multiple of 4; mask rows still span the whole vocabulary) — and the ranks trade one
+   * (score, token id) candidate per row through the symmetric buffer (bcg_tp_symm_create / _open)
+   * inside the kernel; every rank ends with the same token and does the same bookkeeping.
+   * B <= 128.  0 or 1 = single GPU. */
+  int tp_rank, tp_size;
+  int vocab_base;
 } bcg_sampler_args;
 
 /* Launches the sampler described above on `stream` (stands in for xgrammar's mask apply + vLLM's
@@ -235,20 +248,36 @@ int bcg_mask_sample(const bcg_sampler_args* args, void* stream);
 /* Tensor parallelism (Qwen3-32B TP=8, Mistral-22B TP=2 in the reference's presets): one process per
  * GPU, one NCCL communicator per process.  Rank 0 obtains an id with bcg_tp_unique_id, ships the
  * 128 bytes to the other ranks by any means, everyone calls bcg_tp_init (collective).  The model
- * steps then all-reduce the outputs of the row-parallel o / down projections (2 per layer) and
- * all-gather the vocab-parallel logits, standing in for vLLM's TP collectives
+ * steps then all-reduce the outputs of the row-parallel o / down projections (2 per layer); the
+ * vocab-parallel logits stay sharded and the sampler exchanges one candidate per row, standing in
+ * for vLLM's TP collectives
  * (vllm_agent.py:131,141-142).  libnccl.so.2 is resolved at run time. */
 int bcg_tp_unique_id(void* out_128_bytes /* host */);
 int bcg_tp_init(const void* id_128_bytes /* host */, int rank, int size);
 int bcg_tp_shutdown(void);
-/* Optional fast path for the DECODE step: a symmetric buffer every rank of the replica maps
- * (cudaIpc over NVLink).  With it the two per-layer all-reduces are fused into the norm kernel
- * that follows them (peer loads + flags, no NCCL launch); without it the decode step uses NCCL.
- * create: cudaMalloc's `bytes` (the only allocation this library ever makes; freed by
+/* The symmetric buffer every rank of the replica maps (cudaIpc over NVLink).  It carries the
+ * sampler's per-row candidate exchange (bcg_sampler_args.tp_size > 1) and, when
+ * bcg_workspace.tp_region_floats > 0, the decode step's two per-layer all-reduces, fused into the
+ * norm-statistics kernel that follows each row-parallel projection (bcg_tp_add_norm_stats: pushes
+ * over NVLink + flags, no NCCL launch); with tp_region_floats == 0 the decode step all-reduces with
+ * NCCL.  create: cudaMalloc's `bytes` (the only allocation this library ever makes; freed by
  * bcg_tp_shutdown) and returns the 64-byte IPC handle; open: takes all ranks' handles in rank
- * order.  bytes = 4 * (256 + 2 * tp_region_floats) with tp_region_floats as in bcg_workspace. */
+ * order.  bytes = bcg_tp_symm_bytes_for(region, size) = 4 * (32768 + 2 * size * region) with
+ * region = tp_region_floats >= B_max * d_model (0 if only the sampler uses the buffer). */
+long long bcg_tp_symm_bytes_for(long long region_floats, int size);
 int bcg_tp_symm_create(long long bytes, void* handle_out_64_bytes /* host */);
 int bcg_tp_symm_open(const void* handles_size_x_64_bytes /* host */, int rank, int size);
+/* Tensor-parallel counterpart of bcg_add_norm_stats (decode, T <= 128): `partials` are THIS rank's
+ * n_partials fp32 split-K slabs [T, d] of a row-parallel projection (o_proj / down_proj); the kernel
+ * adds them, exchanges the reduced [T, d] message with the other ranks through the symmetric buffer
+ * (slot 0 or 1, alternate between consecutive calls), adds the ranks' contributions in rank order
+ * (bit-identical on every rank), then residual += sum, xn = bf16(residual * w) and
+ * sumsq[s * 128 + t] as bcg_add_norm_stats.  Collective: every rank of the replica must make the same
+ * sequence of calls.  Stands in for vLLM's tensor_model_parallel_all_reduce after RowParallelLinear
+ * + `_C.fused_add_rms_norm`. */
+int bcg_tp_add_norm_stats(float* residual, const float* partials, int n_partials, long long partial_stride,
+                          const float* w, void* xn, float* sumsq, int slot, long long region_floats, int T,
+                          int d, void* stream);
 
 /* Whole-model steps: the layer stack launched from C++ on one stream so a decode step is one
  * host call (captured into a CUDA graph by the engine).  See DESIGN.md §4. */
@@ -288,10 +317,10 @@ typedef struct bcg_workspace {
   float* attn_scratch_ml;
   int* attn_counters;  /* int32 [B_max * n_kv_heads], zero-initialised once */
   int max_splits;
-  float* logits;      /* fp32 [B_max, vocab]; with TP: [tp][B][vocab/tp] as all-gathered */
-  float* logits_local; /* fp32 [B_max, vocab/tp], only with TP */
-  long long tp_region_floats; /* > 0: fused peer-memory all-reduce in decode; floats per slot of the
-                                 symmetric buffer, >= max(splits_o, splits_down) * B_max * d_model */
+  float* logits;      /* fp32 [B_max, vocab] (with TP: this rank's vocabulary shard, vocab = shard size) */
+  float* logits_local; /* unused (kept for layout compatibility) */
+  long long tp_region_floats; /* > 0: fused peer-memory all-reduce in decode; floats per (slot, source
+                                 rank) region of the symmetric buffer, >= B_max * d_model */
   void* xn_last;      /* bf16 [B_max, d_model] */
   int T_max, B_max;
   /* decode norm fusion (bcg_gemm_bf16_tn_fused); both NULL = separate add_rmsnorm kernels */

@@ -5,6 +5,7 @@ same bf16-valued inputs; tolerances are written next to each comparison.  The sa
 work and must match oracle/sampler.py exactly (see test_gpu_sampler.py).
 """
 import math
+import os
 
 import pytest
 import torch
@@ -638,12 +639,16 @@ def test_decode_attn_batch_invariance():
 
 @pytest.mark.parametrize("H,HKV,spec", [
     (4, 2, [(0, 1)]),                       # single token, no prefix
-    (4, 2, [(0, 64), (0, 65), (0, 17)]),    # tile boundaries
+    (4, 2, [(0, 64), (0, 65), (0, 17)]),    # ragged rows inside one tile
+    (4, 2, [(0, 128), (0, 129), (0, 127), (0, 257)]),   # query-tile / KV-block boundaries
     (16, 8, [(0, 200), (48, 130), (160, 1)]),  # cached prefixes (multiples of the page size)
     (40, 8, [(416, 1300), (0, 700)]),
+    (8, 1, [(112, 16), (1008, 40), (2032, 300)]),       # prefix ends 16 short of a KV block; G = 8
+    (48, 8, [(0, 1700)]),                               # Mistral head layout, G = 6, 14 KV blocks
 ])
 def test_prefill_attn_paged(H, HKV, spec):
     """spec: list of (cached_prefix_len, new_tokens)."""
+    TILE = 64 if os.environ.get("BCG_PREFILL_ATTN_LEGACY") else 128
     lib = _lib()
     G = H // HKV
     lens = [c + n for c, n in spec]
@@ -653,13 +658,13 @@ def test_prefill_attn_paged(H, HKV, spec):
     tiles = []
     row = 0
     for b, (c, n) in enumerate(spec):
-        for r0 in range(0, n, 64):
-            tiles.append([b, row + r0, c + r0, min(64, n - r0)])
+        for r0 in range(0, n, TILE):
+            tiles.append([b, row + r0, c + r0, min(TILE, n - r0)])
         row += n
     ti = torch.tensor(tiles, device=DEV, dtype=torch.int32)
     out = torch.full((T, H * 128), float("nan"), device=DEV, dtype=torch.bfloat16)
     L.check(lib.bcg_prefill_attn_paged(q.data_ptr(), cache.data_ptr(), bt.data_ptr(), bt.shape[1],
-                                       ti.data_ptr(), len(tiles), out.data_ptr(), H, HKV, 16,
+                                       ti.data_ptr(), len(tiles), out.data_ptr(), T, H, HKV, 16,
                                        1.0 / math.sqrt(128), L.stream_ptr()))
     torch.cuda.synchronize()
     row = 0
