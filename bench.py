@@ -23,6 +23,15 @@ Printed JSON (one line, rank 0):
              live with CUDA events over all 40 layers' weights (1.4e10 B > L2)
   decode  whole-step decode roofline (weights + KV bytes per step / step time)
   cpu_baseline  the CPU oracle (transformers fp32 + xgrammar) timed on this host, bounded sample
+                (`extrapolated: true`: a 2-layer slice scaled to the full depth and retry schedule)
+  fixed   the same metric on a FIXED schedule (every call of a round runs all rows to max_tokens,
+          forced tokens "{" + blanks — the retry storm with nothing ever validating): identical work
+          in every run, on every rank and in every round, so it can be compared round over round
+          and its 1->N curve measures the machine rather than each game's retry luck
+  ranks   per-rank device / wall seconds of the faithful region (value uses the max, as the
+          contract says; value_mean_over_ranks is beside it)
+  single_game (N > 1)  ONE game whose rows are sharded over the N replicas (dp.run_sharded): the
+          latency half of SURVEY.md §8e; `value` above is the aggregate half (one game per replica)
 """
 from __future__ import annotations
 
@@ -110,6 +119,27 @@ def agent_step(agent, rnd, counters):
               valid_vote, counters)
 
 
+def fixed_round(agent, engine, rnd):
+    """One game round on the FIXED schedule: MAX_RETRIES batched attempts per phase, every row
+    teacher-forced through "{" + blanks (valid in all four reference grammars, never accepting),
+    so every call runs all its rows to max_tokens.  Returns the number of engine calls."""
+    from byzantine_consensus_llm_agents_b200.engine import Request
+    tk = engine.tk
+    brace, blank = tk.encode("{", False), tk.encode(" ", False)
+    assert len(brace) == 1 and len(blank) == 1, "tokenizer must have single tokens for '{' and ' '"
+    calls = 0
+    for phase, temp, mt in (("decide", LLM["temperature_decide"], LLM["max_tokens_decide"]),
+                            ("vote", LLM["temperature_vote"], LLM["max_tokens_vote"])):
+        forced = brace + blank * (mt - 1)
+        for _ in range(MAX_RETRIES):
+            reqs = [Request(agent._format_chat_prompt(s, u), sc, temp, mt, forced=forced)
+                    for s, u, sc in rnd[phase]["prompts"]]
+            res = engine.generate(reqs)
+            assert all(len(r.token_ids) == mt for r in res)
+            calls += 1
+    return calls
+
+
 class ClockSampler:
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -184,11 +214,13 @@ def kernel_roofline(engine, B: int, hbm_peak: float, peak_kind: str):
     ms = e0.elapsed_time(e1) / (reps * layers)
     alg_bytes = N * K * 2 + B * K * 2 + (B * (N // 2) * 2 if splits == 1 else splits * B * N * 4)
     achieved = alg_bytes / (ms * 1e-3) / 1e9
-    traffic = None
+    traffic, traffic_source = None, None
     prof = ROOT / "profiles" / "r01_gemm_decode_traffic.json"
     if prof.exists():
         try:
             traffic = json.loads(prof.read_text()).get("dram_bytes_per_launch")
+            traffic_source = ("profiles/r01_gemm_decode_traffic.json (one ncu --set full capture of this kernel "
+                              "and shape, dram__bytes_read.sum + dram__bytes_write.sum; not re-measured in this run)")
         except Exception:
             traffic = None
     return {"kernel": f"gemm_tcgen05_kernel<BN={16 if B <= 16 else 32 if B <= 32 else 64 if B <= 64 else 128}> "
@@ -196,6 +228,7 @@ def kernel_roofline(engine, B: int, hbm_peak: float, peak_kind: str):
                       f"{', back-to-back launches with programmatic dependent launch' if gflags else ''})",
             "bound": "hbm", "achieved": round(achieved, 1), "peak": hbm_peak, "peak_kind": peak_kind,
             "unit": "GB/s", "frac": round(achieved / hbm_peak, 4), "traffic": traffic,
+            "traffic_source": traffic_source,
             "us_per_launch": round(ms * 1e3, 2), "algorithmic_bytes_per_launch": alg_bytes}
 
 
@@ -255,7 +288,8 @@ def cpu_baseline(model_key: str, rounds, n_agents: int, layers_sample: int = 2, 
     per_agent = MAX_RETRIES * (n_prompt * prefill_full_tok + LLM["max_tokens_decide"] * step_full) + \
         MAX_RETRIES * (n_vote * prefill_full_tok + LLM["max_tokens_vote"] * step_full)
     return {"value": round(1.0 / per_agent, 6), "unit": "agent-steps/s", "cores": threads,
-            "host_cpus": os.cpu_count(), "kind": "port",
+            "host_cpus": os.cpu_count(), "kind": "port", "extrapolated": True,
+            "measured_sample_s": round(t_sample, 2),
             "decode_tok_s": round(1.0 / step_full, 3),
             "sample": (f"oracle engine (transformers fp32 + xgrammar + oracle sampler), {layers_sample}-layer "
                        f"full-width {full.name}: {prefill_tokens}-token prefill + {decode_steps} guided decode "
@@ -273,6 +307,10 @@ def main():
     ap.add_argument("--honest", type=int, default=8)
     ap.add_argument("--byzantine", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--fixed-rounds", type=int, default=1,
+                    help="extra rounds on the fixed (all rows to max_tokens) schedule, reported under 'fixed'")
+    ap.add_argument("--single-game-steps", type=int, default=1,
+                    help="N > 1: extra rounds of ONE game with rows sharded over the replicas ('single_game')")
     ap.add_argument("--tp", type=int, default=1,
                     help="tensor_parallel_size of each replica (ranks beyond the first are spawned by "
                          "the adapter, like vLLM's mp executor); use with --gpus == --tp")
@@ -356,11 +394,61 @@ def main():
     dev_s = d["prefill_s"] + d["decode_s"]
 
     t = torch.tensor([wall, dev_s], dtype=torch.float64, device="cuda")
+    per_rank = [t.clone() for _ in range(world)]
     if world > 1:
         dist.barrier()
+        dist.all_gather(per_rank, t)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     wall_max, dev_max = t.tolist()
     total_agent_steps = n_agents * a.steps * world
+    rank_wall = [round(float(x[0]), 3) for x in per_rank]
+    rank_dev = [round(float(x[1]), 3) for x in per_rank]
+
+    # ---- the fixed schedule (identical work everywhere; see the module docstring)
+    fixed = None
+    if a.tp == 1 and a.fixed_rounds > 0:
+        engine.reset_prefix_cache()
+        fixed_round(agent, engine, rounds[0])                       # warm-up (graphs of this shape)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        f0 = dict(engine.stats)
+        for i in range(a.fixed_rounds):
+            fixed_round(agent, engine, rounds[(1 + i) % len(rounds)])
+        torch.cuda.synchronize()
+        f1 = dict(engine.stats)
+        fd = {k: f1[k] - f0[k] for k in f1}
+        ft = torch.tensor([fd["prefill_s"] + fd["decode_s"]], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(ft, op=dist.ReduceOp.MAX)
+        fixed = {"value": round(n_agents * a.fixed_rounds * world / float(ft[0]), 4), "unit": "agent-steps/s",
+                 "rounds": a.fixed_rounds, "decode_steps_per_round": fd["decode_steps"] / a.fixed_rounds,
+                 "rows_per_step": round(fd["generated_tokens"] / max(1, fd["decode_steps"]), 2),
+                 "decode_ms_per_step": round(1e3 * fd["decode_s"] / max(1, fd["decode_steps"]), 3),
+                 "prefill_s_per_round": round(fd["prefill_s"] / a.fixed_rounds, 3),
+                 "schedule": f"{MAX_RETRIES} batched attempts per phase, all {n_agents} rows forced to max_tokens"}
+
+    # ---- ONE game, rows sharded over the replicas (latency half of SURVEY.md §8e)
+    single = None
+    if world > 1 and a.tp == 1 and a.single_game_steps > 0:
+        engine.reset_prefix_cache()
+        engine.base_seed, engine.calls = 4242, 0                    # every replica plays the SAME game
+        agent.llm.data_parallel = True
+        cs = dict(calls=0, rows=0, ok=0, abstain=0)
+        agent_step(agent, rounds[0], cs)                            # warm-up (graphs of the sharded shapes)
+        torch.cuda.synchronize()
+        dist.barrier()
+        t0 = time.perf_counter()
+        for i in range(a.single_game_steps):
+            agent_step(agent, rounds[(1 + i) % len(rounds)], cs)
+        torch.cuda.synchronize()
+        st = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        dist.all_reduce(st, op=dist.ReduceOp.MAX)
+        agent.llm.data_parallel = False
+        single = {"value": round(n_agents * a.single_game_steps / float(st[0]), 4), "unit": "agent-steps/s",
+                  "steps": a.single_game_steps, "ms_per_step": round(1e3 * float(st[0]) / a.single_game_steps, 1),
+                  "what": f"one game, its rows split round-robin over {world} replicas (no device collective; "
+                          "texts gathered host-side); compare with e2e / n_gpus"}
 
     if rank == 0:
         cfg = engine.cfg
@@ -393,6 +481,10 @@ def main():
                         "achieved": round(pf_flops / max(1e-9, d["prefill_s"]) / 1e12, 1), "peak": tf_peak,
                         "unit": "TFLOP/s (GEMM flops / whole prefill time incl. attention, norms, sampling)",
                         "frac": round(pf_flops / max(1e-9, d["prefill_s"]) / 1e12 / tf_peak, 4)},
+            "value_mean_over_ranks": round(n_agents * a.steps * world * world / max(1e-9, sum(rank_dev)), 4),
+            "ranks": {"device_s": rank_dev, "wall_s": rank_wall,
+                      "note": "one independently seeded game per rank; value divides by the slowest rank"},
+            "fixed": fixed, "single_game": single,
             "per_step": {"engine_calls": counters["calls"] / a.steps, "rows": counters["rows"] / a.steps,
                          "valid": counters["ok"] / a.steps, "abstain": counters["abstain"] / a.steps,
                          "generated_tokens": gen / a.steps, "decode_steps": steps / a.steps,

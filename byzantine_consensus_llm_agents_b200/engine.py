@@ -38,7 +38,8 @@ from .model import ModelConfig, ModelHandle, Weights
 PAGE = 16
 SPLIT_TOKENS = 256
 MAX_GRAMMARS = 64
-POLL_EVERY = 16
+POLL_EVERY = 8      # tensor-parallel engines: steps between two synchronised looks at the active-row count
+IN_FLIGHT = 2       # single-GPU engines: decode steps queued ahead of the one whose result the host has seen
 # query rows per prefill-attention CTA (bcg_prefill_attn_paged)
 PREFILL_TILE = 64 if __import__("os").environ.get("BCG_PREFILL_ATTN_LEGACY") else 128
 
@@ -243,15 +244,35 @@ class Engine:
         self.kv_layers = [z(kv_pages, 2, lc.n_kv_heads, PAGE, 128) for _ in range(cfg.n_layers)]
         self.pool = PagePool(kv_pages)
         self.model = ModelHandle(weights, self.kv_layers, PAGE, tp_size)
-        # ---- per-row device state (bcg_sampler_args)
-        self.row = dict(
-            grammar_id=z(B, dt=i32), state=z(B, dt=i32), temperature=z(B, dt=f32), seed=z(B, 2, dt=i32),
-            max_tokens=z(B, dt=i32), n_out=z(B, dt=i32), finished=z(B, dt=i32),
+        # ---- per-row device state (bcg_sampler_args).  Everything the host writes at the start of a
+        # call lives in ONE int32 block with a pinned host mirror, so a call costs one H2D copy
+        # instead of one per field.
+        fields = [("grammar_id", 1), ("state", 1), ("temperature", 1), ("seed", 2), ("max_tokens", 1),
+                  ("n_out", 1), ("finished", 1), ("seq_lens", 1), ("block_table", self.max_blocks)]
+        words = sum(w for _, w in fields) * B
+        self._state_dev = z(words, dt=i32)
+        self._state_host = torch.zeros(words, dtype=i32).pin_memory()
+        self.row, self.row_host, off = {}, {}, 0
+        for name, w in fields:
+            dv, hv = self._state_dev[off:off + w * B], self._state_host[off:off + w * B].numpy()
+            if w > 1:
+                dv, hv = dv.view(B, w), hv.reshape(B, w)
+            if name == "temperature":
+                dv, hv = dv.view(f32), hv.view(np.float32)
+            self.row[name], self.row_host[name] = dv, hv
+            off += w * B
+        self.row.update(
             out_tokens=z(B, self.max_steps, dt=i32), chosen=z(B, self.max_steps, dt=i32),
             forced=torch.full((B, self.max_steps), -1, dtype=i32, device=self.dev),
-            next_ids=z(B, dt=i32), positions=z(B, dt=i32), seq_lens=z(B, dt=i32), slot_map=z(B, dt=i32),
-            block_table=z(B, self.max_blocks, dt=i32), n_active=z(1, dt=i32))
+            next_ids=z(B, dt=i32), positions=z(B, dt=i32), slot_map=z(B, dt=i32))
+        # Number of unfinished rows: the sampler's bookkeeping kernel writes it straight into pinned
+        # HOST memory (mapped into the device's address space), so the host reads it without a copy.
         self.n_active_host = torch.zeros(1, dtype=i32).pin_memory()
+        self.row["n_active"] = self.n_active_host
+        # ---- prefill staging: ids | positions | slots | last rows | tiles | block table, one copy per group
+        self._pf_cap = (3 * self.T_max, B, 4 * (self.T_max // PREFILL_TILE + B), B * self.max_blocks, 32)
+        self._pf_dev = z(sum(self._pf_cap), dt=i32)
+        self._pf_host = torch.zeros(sum(self._pf_cap), dtype=i32).pin_memory()
         # ---- tokenizer / grammar tables on the device
         tok_bytes = G.grammar_token_bytes(tokenizer)
         lens = np.fromiter((len(x) for x in tok_bytes), np.int64, count=cfg.vocab)
@@ -420,17 +441,20 @@ class Engine:
         gids = [self.grammar_index(q.schema) for q in reqs]
         seeds = np.array([tuple(q.seed) if q.seed is not None else row_seed(self.base_seed, self.calls, row0 + b)
                           for b, q in enumerate(reqs)], np.uint32)
-        host_rows = dict(
-            grammar_id=np.array(gids, np.int32), state=np.zeros(B, np.int32),
-            temperature=np.array([q.temperature for q in reqs], np.float32),
-            max_tokens=np.array([q.max_tokens for q in reqs], np.int32),
-            n_out=np.zeros(B, np.int32), finished=np.zeros(B, np.int32),
-            seq_lens=np.array([len(x) for x in ids_list], np.int32))
-        for k, v in host_rows.items():
-            r[k][:B].copy_(torch.from_numpy(v), non_blocking=False)
-        r["seed"][:B].copy_(torch.from_numpy(seeds.view(np.int32)))
-        r["block_table"][:B].copy_(torch.from_numpy(bt))
-        self.stats["h2d_bytes"] += sum(v.nbytes for v in host_rows.values()) + seeds.nbytes + bt.nbytes
+        # the previous call's copy out of the pinned mirror has long completed (every call ends with
+        # a device synchronisation), so the mirror may be rewritten in place
+        h = self.row_host
+        h["grammar_id"][:B] = gids
+        h["state"][:B] = 0
+        h["temperature"][:B] = [q.temperature for q in reqs]
+        h["max_tokens"][:B] = [q.max_tokens for q in reqs]
+        h["n_out"][:B] = 0
+        h["finished"][:B] = 0
+        h["seq_lens"][:B] = [len(x) for x in ids_list]
+        h["seed"][:B] = seeds.view(np.int32).reshape(B, 2)
+        h["block_table"][:B] = bt
+        self._state_dev.copy_(self._state_host, non_blocking=True)     # ONE copy for all per-row state
+        self.stats["h2d_bytes"] += self._state_host.numel() * 4
         if use_forced:
             f = np.full((B, self.max_steps), -1, np.int32)
             for b, q in enumerate(reqs):
@@ -482,21 +506,45 @@ class Engine:
                 steps += 1
                 self.stats["gpu_launches"] += per_step
                 graph = self._graph_for(B, max_splits, use_forced)
-            while steps < max_new - 1 and not done:
-                n = min(POLL_EVERY, max_new - 1 - steps)
-                for _ in range(n):
-                    if graph is not None:
-                        graph.replay()
-                    else:
-                        self._decode_step(B, max_splits, use_forced)
-                        if self.debug_logits is not None:
-                            self.debug_logits.append(self._logits_rows(B))
-                steps += n
-                self.stats["gpu_launches"] += n * per_step
-                self.n_active_host.copy_(r["n_active"], non_blocking=True)
-                torch.cuda.current_stream().synchronize()
-                done = int(self.n_active_host[0]) == 0
-                self.stats["d2h_bytes"] += 4
+            def one_step():
+                if graph is not None:
+                    graph.replay()
+                else:
+                    self._decode_step(B, max_splits, use_forced)
+                    if self.debug_logits is not None:
+                        self.debug_logits.append(self._logits_rows(B))
+
+            if self.tp_size == 1:
+                # The bookkeeping kernel of every step leaves the number of unfinished rows in pinned
+                # host memory.  The host keeps at most IN_FLIGHT steps queued: before launching step
+                # k it waits for step k - IN_FLIGHT and looks at the counter, so a call whose rows
+                # have all finished runs at most IN_FLIGHT dead steps (it used to poll every 16
+                # steps: ~8 dead steps of 5.5 ms on average for every call that ends early) and the
+                # GPU never waits for the host (one step is queued behind the running one).
+                ring = [torch.cuda.Event() for _ in range(IN_FLIGHT + 1)]
+                launched = 0
+                while steps < max_new - 1:
+                    one_step()
+                    ring[launched % len(ring)].record()
+                    launched += 1
+                    steps += 1
+                    if launched >= IN_FLIGHT:
+                        ring[(launched - IN_FLIGHT) % len(ring)].synchronize()
+                        if int(self.n_active_host[0]) == 0:
+                            break
+                self.stats["gpu_launches"] += launched * per_step
+            else:
+                # Tensor parallelism: every rank must stop after the SAME step (a rank that ran one
+                # step more would wait for peers that never come), so the ranks decide at fixed step
+                # counts on a fully synchronised counter, which is identical everywhere.
+                while steps < max_new - 1 and not done:
+                    n = min(POLL_EVERY, max_new - 1 - steps)
+                    for _ in range(n):
+                        one_step()
+                    steps += n
+                    self.stats["gpu_launches"] += n * per_step
+                    torch.cuda.current_stream().synchronize()
+                    done = int(self.n_active_host[0]) == 0
         ev2.record()
         torch.cuda.synchronize()
         t_host1 = time.perf_counter()
@@ -551,10 +599,23 @@ class Engine:
             row += n
             last.append(row - 1)
         T, n_seqs = row, b1 - b0
-        t = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.int32)).to(dev)
-        d_ids, d_pos, d_slots = t(ids), t(np.concatenate(pos)), t(np.concatenate(slots))
-        d_tiles, d_last, d_bt = t(np.array(tiles)), t(last), t(bt[b0:b1])
-        self.stats["h2d_bytes"] += sum(x.numel() * 4 for x in (d_ids, d_pos, d_slots, d_tiles, d_last, d_bt))
+        # one pinned staging block, one H2D copy per group: ids | positions | slots | last | tiles | bt.
+        # A group's copy must have left the pinned block before the next group refills it.
+        if getattr(self, "_pf_event", None) is not None:
+            self._pf_event.synchronize()
+        hs, o0 = self._pf_host.numpy(), 0
+        views = []
+        for arr in (ids, np.concatenate(pos), np.concatenate(slots), last, np.array(tiles).reshape(-1),
+                    bt[b0:b1].reshape(-1)):
+            a = np.asarray(arr, dtype=np.int32)
+            hs[o0:o0 + a.size] = a
+            views.append(self._pf_dev[o0:o0 + a.size])
+            o0 += (a.size + 3) // 4 * 4        # keep every array 16-byte aligned
+        self._pf_dev[:o0].copy_(self._pf_host[:o0], non_blocking=True)
+        self._pf_event = torch.cuda.Event()
+        self._pf_event.record()
+        d_ids, d_pos, d_slots, d_last, d_tiles, d_bt = views
+        self.stats["h2d_bytes"] += o0 * 4
         # this group's last-token logits go straight to rows b0..b1 of the row-indexed buffer
         base = self.buf["logits"].data_ptr()
         self.ws.logits = base + b0 * self.lcfg.vocab * 4
@@ -567,7 +628,6 @@ class Engine:
         finally:
             self.ws.logits = base
         self.stats["gpu_launches"] += cfg.n_layers * 8 + 2
-        self._keepalive = (d_ids, d_pos, d_slots, d_tiles, d_last, d_bt)
 
     # ------------------------------------------------------------------ misc
     def reset_prefix_cache(self) -> None:

@@ -20,7 +20,7 @@ def so():
 
 
 def test_every_declared_symbol_is_exported(so):
-    declared = set(re.findall(r"^\s*(?:int|const char\*)\s+(bcg_\w+)\s*\(", HEADER, flags=re.M))
+    declared = set(re.findall(r"^\s*(?:int|long long|const char\*)\s+(bcg_\w+)\s*\(", HEADER, flags=re.M))
     assert len(declared) >= 14
     assert declared == set(L.EXPORTED), declared ^ set(L.EXPORTED)
     for name in declared:

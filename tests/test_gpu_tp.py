@@ -1,6 +1,8 @@
-"""Tensor parallelism: TP=2 must give the fp32 CPU forward's logits within the same
-2e-2 tolerance as TP=1, and — greedy, under a grammar — the same token streams as TP=1.
-Needs two GPUs; skipped otherwise (the single-GPU CI box runs everything else)."""
+"""Tensor parallelism: TP=2 (and TP=8 on an 8-GPU box) must give the fp32 CPU
+forward's logits within the same 2e-2 tolerance as TP=1, and — greedy, under a grammar — the same
+token streams on every rank and (up to near-ties) as TP=1.  Covers the fused path (all-reduce inside
+bcg_tp_add_norm_stats over NVLink peer memory, vocab-parallel sampling with one candidate per row
+exchanged) and the NCCL all-reduce path.  Needs >= 2 GPUs; skipped otherwise."""
 import os
 import socket
 
@@ -36,6 +38,8 @@ def _worker(rank, size, port, family, fused, ret):
         if family == "mistral":
             cfg = ModelConfig("tp-mistral", n_layers=2, d_model=512, n_heads=8, n_kv_heads=2, d_ff=1024,
                               vocab=4096, qk_norm=False, family="mistral")
+        elif size > 4:
+            cfg = ModelConfig("tp8-qwen3", n_layers=3, d_model=512, n_heads=16, n_kv_heads=8, d_ff=2048, vocab=8192)
         else:
             cfg = ModelConfig("tp-qwen3", n_layers=3, d_model=512, n_heads=8, n_kv_heads=4, d_ff=1536, vocab=8192)
         hf = build_hf_model(cfg, seed=0)
@@ -59,7 +63,10 @@ def _worker(rank, size, port, family, fused, ret):
                   "required": ["decision"], "additionalProperties": False}
         free = eng.generate([Request("", schema, 0.0, 24, prompt_ids=p) for p in prompts])
         free2 = eng.generate([Request("", schema, 0.0, 24, prompt_ids=p) for p in prompts])   # CUDA graph + prefix hits
-        out = {"tokens": [r.token_ids for r in free], "tokens2": [r.token_ids for r in free2]}
+        # sampled (T = 0.7, fixed Philox keys): the vocab-parallel race must pick what one GPU picks
+        samp = eng.generate([Request("", None, 0.7, 16, prompt_ids=p, seed=(11 + i, 5)) for i, p in enumerate(prompts)])
+        out = {"tokens": [r.token_ids for r in free], "tokens2": [r.token_ids for r in free2],
+               "sampled": [r.token_ids for r in samp]}
         if rank == 0:
             worst = 0.0
             for b, (p, f) in enumerate(zip(prompts, forced)):
@@ -71,6 +78,8 @@ def _worker(rank, size, port, family, fused, ret):
                           device="cuda:0")
             out["solo"] = [r.token_ids for r in solo.generate([Request("", schema, 0.0, 24, prompt_ids=p)
                                                                for p in prompts])]
+            out["solo_sampled"] = [r.token_ids for r in solo.generate(
+                [Request("", None, 0.7, 16, prompt_ids=p, seed=(11 + i, 5)) for i, p in enumerate(prompts)])]
         ret[rank] = out
         eng.close()
         torch.cuda.synchronize()
@@ -81,15 +90,20 @@ def _worker(rank, size, port, family, fused, ret):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("family,fused", [("qwen3", True), ("mistral", True), ("qwen3", False)],
-                         ids=["qwen3-fused", "mistral-fused", "qwen3-nccl"])
-def test_tp2_matches_oracle_and_tp1(family, fused):
-    """fused = decode all-reduces inside the norm kernels over peer memory; otherwise NCCL."""
+@pytest.mark.parametrize("size,family,fused", [(2, "qwen3", True), (2, "mistral", True), (2, "qwen3", False),
+                                               (8, "qwen3", True), (4, "qwen3", True)],
+                         ids=["tp2-qwen3-fused", "tp2-mistral-fused", "tp2-qwen3-nccl", "tp8-qwen3-fused",
+                              "tp4-qwen3-fused"])
+def test_tp_matches_oracle_and_tp1(size, family, fused):
+    """fused = decode all-reduces inside the norm-statistics kernels over peer memory; otherwise NCCL."""
+    if torch.cuda.device_count() < size:
+        pytest.skip(f"needs {size} GPUs")
     mgr = mp.Manager()
     ret = mgr.dict()
-    mp.spawn(_worker, args=(2, _free_port(), family, fused, ret), nprocs=2, join=True)
+    mp.spawn(_worker, args=(size, _free_port(), family, fused, ret), nprocs=size, join=True)
     assert ret[0]["worst"] <= LOGIT_TOL, ret[0]["worst"]
-    assert ret[0]["tokens"] == ret[1]["tokens"]              # replicated sampling agrees across ranks
+    for rk in range(1, size):                                # every rank ends with the same tokens
+        assert ret[0]["tokens"] == ret[rk]["tokens"] and ret[0]["sampled"] == ret[rk]["sampled"]
     assert ret[0]["tokens2"] == ret[0]["tokens"]             # graph replay + prefix cache: same stream
     # TP changes the summation order of the row-parallel projections; streams may part only at a
     # near-tie, so require a long common prefix rather than equality
@@ -98,4 +112,9 @@ def test_tp2_matches_oracle_and_tp1(family, fused):
         while common < min(len(a), len(b)) and a[common] == b[common]:
             common += 1
         assert common >= min(len(a), len(b)) // 2, (a, b)
-    print(f"{family} fused={fused}: TP=2 worst |dlogit| {ret[0]['worst']:.4f}")
+    for a, b in zip(ret[0]["sampled"], ret[0]["solo_sampled"]):
+        common = 0
+        while common < min(len(a), len(b)) and a[common] == b[common]:
+            common += 1
+        assert common >= 4, (a, b)     # same Philox stream and masks: the race starts out identical
+    print(f"{family} fused={fused}: TP={size} worst |dlogit| {ret[0]['worst']:.4f}")
