@@ -134,7 +134,7 @@ def fixed_round(agent, engine, rnd):
         for _ in range(MAX_RETRIES):
             reqs = [Request(agent._format_chat_prompt(s, u), sc, temp, mt, forced=forced)
                     for s, u, sc in rnd[phase]["prompts"]]
-            res = engine.generate(reqs)
+            res = (agent.llm.tp.generate if agent.llm.tp is not None else engine.generate)(reqs)
             assert all(len(r.token_ids) == mt for r in res)
             calls += 1
     return calls
@@ -312,8 +312,9 @@ def main():
     ap.add_argument("--single-game-steps", type=int, default=1,
                     help="N > 1: extra rounds of ONE game with rows sharded over the replicas ('single_game')")
     ap.add_argument("--tp", type=int, default=1,
-                    help="tensor_parallel_size of each replica (ranks beyond the first are spawned by "
-                         "the adapter, like vLLM's mp executor); use with --gpus == --tp")
+                    help="tensor_parallel_size of each replica.  Plain `python bench.py --gpus T --tp T`: the "
+                         "adapter spawns ranks 1..T-1 (like vLLM's mp executor).  Under torchrun with N ranks: "
+                         "N/T replicas of T consecutive ranks each, one game per replica (TP composed with DP)")
     ap.add_argument("--pdl", type=int, default=int(os.environ.get("BCG_B200_PDL", "1")),
                     help="programmatic dependent launch for the decode step (1 = on)")
     a = ap.parse_args()
@@ -328,7 +329,9 @@ def main():
                           "one game round per step (decide T=0.5/300 tok + vote T=0.3/200 tok, reference "
                           "retry schedule), recorded steady-state reference prompts",
               "agents": n_agents, "rounds_recorded": len(rounds), "pdl": bool(a.pdl),
-              "parallelism": (f"tp{a.tp} (one replica, NCCL all-reduce)" if a.tp > 1 else
+              "parallelism": (f"tp{a.tp} x dp{max(1, world // a.tp)} (one game per tensor-parallel replica; decode "
+                              "all-reduces fused into the norm-statistics kernels over NVLink peer memory)"
+                              if a.tp > 1 else
                               f"dp{world} (one independent game per GPU)" if world > 1 else "single GPU"),
               "l2": "per-step inputs (all layer weights, tens of GB per decode step) exceed the 126 MB L2"}
 
@@ -365,8 +368,30 @@ def main():
     model_config = {"max_model_len": 8192, "gpu_memory_utilization": 0.9, "tensor_parallel_size": 1,
                     "max_num_seqs": 4, "disable_qwen3_thinking": True, "device": f"cuda:{local_rank}",
                     "seed": 1000 + rank, "engine_max_rows": max(16, n_agents), "pdl": bool(a.pdl)}
+    # collectives of the measurement itself: the default NCCL group, or — when tensor-parallel
+    # replicas are cut out of the torchrun world — a gloo group of the replica leaders
+    leaders, lg, red_dev = world, None, "cuda"
     if a.tp > 1:
         model_config["tensor_parallel_size"] = a.tp
+        if world > 1:
+            from byzantine_consensus_llm_agents_b200 import tp as TP
+            dist.barrier()                                           # NCCL communicator over all ranks
+            group, pos, replica, leader = TP.replica_groups(a.tp)
+            leaders = world // a.tp
+            lg = dist.new_group(list(range(0, world, a.tp)), backend="gloo")
+            red_dev = "cpu"
+            model_config.update(tp_group=group, tp_leader=leader, device=f"cuda:{local_rank - pos}",
+                                seed=1000 + replica)
+            if pos > 0:
+                TP.serve_worker(model_name, model_config, pos, a.tp)   # returns when the leader closes
+                dist.barrier()
+                dist.destroy_process_group()
+                return
+
+    def barrier():
+        if world > 1:
+            dist.barrier(group=lg)
+
     t_load = time.perf_counter()
     agent = VA.VLLMAgent("agent_0", model_name, model_config)
     engine = agent.llm.engine
@@ -377,8 +402,7 @@ def main():
     for i in range(a.warmup):
         agent_step(agent, rounds[i % len(rounds)], counters)
     torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
+    barrier()
     counters = dict(calls=0, rows=0, ok=0, abstain=0)
     s0 = dict(engine.stats)
     clocks = ClockSampler(local_rank) if rank == 0 else None
@@ -393,35 +417,35 @@ def main():
     d = {k: s1[k] - s0[k] for k in s1}
     dev_s = d["prefill_s"] + d["decode_s"]
 
-    t = torch.tensor([wall, dev_s], dtype=torch.float64, device="cuda")
-    per_rank = [t.clone() for _ in range(world)]
+    t = torch.tensor([wall, dev_s], dtype=torch.float64, device=red_dev)
+    per_rank = [t.clone() for _ in range(leaders)]
     if world > 1:
-        dist.barrier()
-        dist.all_gather(per_rank, t)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        barrier()
+        dist.all_gather(per_rank, t, group=lg)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=lg)
     wall_max, dev_max = t.tolist()
-    total_agent_steps = n_agents * a.steps * world
+    total_agent_steps = n_agents * a.steps * leaders
     rank_wall = [round(float(x[0]), 3) for x in per_rank]
     rank_dev = [round(float(x[1]), 3) for x in per_rank]
 
     # ---- the fixed schedule (identical work everywhere; see the module docstring)
     fixed = None
-    if a.tp == 1 and a.fixed_rounds > 0:
-        engine.reset_prefix_cache()
+    if a.fixed_rounds > 0:
+        if a.tp == 1:
+            engine.reset_prefix_cache()
         fixed_round(agent, engine, rounds[0])                       # warm-up (graphs of this shape)
         torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
+        barrier()
         f0 = dict(engine.stats)
         for i in range(a.fixed_rounds):
             fixed_round(agent, engine, rounds[(1 + i) % len(rounds)])
         torch.cuda.synchronize()
         f1 = dict(engine.stats)
         fd = {k: f1[k] - f0[k] for k in f1}
-        ft = torch.tensor([fd["prefill_s"] + fd["decode_s"]], dtype=torch.float64, device="cuda")
+        ft = torch.tensor([fd["prefill_s"] + fd["decode_s"]], dtype=torch.float64, device=red_dev)
         if world > 1:
-            dist.all_reduce(ft, op=dist.ReduceOp.MAX)
-        fixed = {"value": round(n_agents * a.fixed_rounds * world / float(ft[0]), 4), "unit": "agent-steps/s",
+            dist.all_reduce(ft, op=dist.ReduceOp.MAX, group=lg)
+        fixed = {"value": round(n_agents * a.fixed_rounds * leaders / float(ft[0]), 4), "unit": "agent-steps/s",
                  "rounds": a.fixed_rounds, "decode_steps_per_round": fd["decode_steps"] / a.fixed_rounds,
                  "rows_per_step": round(fd["generated_tokens"] / max(1, fd["decode_steps"]), 2),
                  "decode_ms_per_step": round(1e3 * fd["decode_s"] / max(1, fd["decode_steps"]), 3),
@@ -463,7 +487,7 @@ def main():
         pf_flops = d["prefill_tokens"] * cfg.prefill_gemm_flops_per_token() / a.tp   # per GPU
         line = {
             "metric": "agent_steps_per_sec", "value": round(total_agent_steps / dev_max, 4),
-            "unit": "agent-steps/s", "n_gpus": world * a.tp, "steps": a.steps, "warmup": a.warmup,
+            "unit": "agent-steps/s", "n_gpus": world if world > 1 else a.tp, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": round(1e3 * wall_max / a.steps, 2), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": config,
@@ -471,7 +495,7 @@ def main():
                     "h2d_bytes_per_step": int(d["h2d_bytes"] / a.steps),
                     "d2h_bytes_per_step": int(d["d2h_bytes"] / a.steps)},
             "gpu_launches": int(d["gpu_launches"]),
-            "decode_tok_s": round(world * gen / max(1e-9, d["decode_s"]), 1),
+            "decode_tok_s": round(leaders * gen / max(1e-9, d["decode_s"]), 1),
             "decode": {"bound": "hbm", "bytes_per_step": int(bytes_per_step), "ms_per_step": round(step_s * 1e3, 3),
                        "rows_per_step": round(avg_rows, 2), "avg_context": int(avg_ctx),
                        "achieved": round(dec_ach, 1), "peak": hbm_peak, "unit": "GB/s",
@@ -481,7 +505,7 @@ def main():
                         "achieved": round(pf_flops / max(1e-9, d["prefill_s"]) / 1e12, 1), "peak": tf_peak,
                         "unit": "TFLOP/s (GEMM flops / whole prefill time incl. attention, norms, sampling)",
                         "frac": round(pf_flops / max(1e-9, d["prefill_s"]) / 1e12 / tf_peak, 4)},
-            "value_mean_over_ranks": round(n_agents * a.steps * world * world / max(1e-9, sum(rank_dev)), 4),
+            "value_mean_over_ranks": round(n_agents * a.steps * leaders * leaders / max(1e-9, sum(rank_dev)), 4),
             "ranks": {"device_s": rank_dev, "wall_s": rank_wall,
                       "note": "one independently seeded game per rank; value divides by the slowest rank"},
             "fixed": fixed, "single_game": single,

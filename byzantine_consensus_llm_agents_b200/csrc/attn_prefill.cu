@@ -91,6 +91,35 @@ __device__ __forceinline__ void tmem_st_wait() {
   asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
 
+// The softmax warps are bound by instruction issue (one slot per sub-partition and clock), so the
+// exponent path uses the cheapest encodings the ISA has: packed two-lane fp32 FMA / ADD
+// (fma.rn.f32x2, add.rn.f32x2 — one issue slot for two elements) and the bare ex2.approx.ftz
+// (exp2f() wraps it in a denormal-range rescue of three more instructions; the arguments here are
+// <= 8 and flush-to-zero at the bottom is exactly what a softmax tail wants).
+__device__ __forceinline__ uint64_t pack_f32x2(uint32_t lo, uint32_t hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack_f32x2(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t fma_f32x2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t add_f32x2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 // MN-major, 128B-swizzled B operand: V as it lies in the cache, [token][head_dim], staged as two
 // 64-column halves of [BN tokens][64] (128-byte rows).  In the canonical MN-major layout
 // ((8,8,m),(8,k)):((1,8,LBO),(64,SBO)) (elements; cute/atom/mma_traits_sm100.hpp) that is: 64
@@ -298,7 +327,7 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_cons
       mbar_wait(pv_done, (j & 1) ^ 1);
       if (j > 0 && __any_sync(0xffffffffu, grow)) {
         tc_fence_after();
-        const float corr = grow ? exp2f(m_run - m_new) : 1.0f;
+        const float corr = grow ? ex2_approx(m_run - m_new) : 1.0f;
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           uint32_t o[32];
@@ -312,21 +341,26 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_cons
         l_run *= corr;
       }
       m_run = m_new;
-      float l_blk = 0.f;
+      const uint64_t scale2 = pack_f32x2(__float_as_uint(scale_log2e), __float_as_uint(scale_log2e));
+      const uint64_t negm2 = pack_f32x2(__float_as_uint(-m_run), __float_as_uint(-m_run));
+      uint64_t l2 = pack_f32x2(0u, 0u);
 #pragma unroll
       for (int c = 0; c < BN / 8; ++c) {   // 8 tokens = one 16-byte chunk of the K-major P tile
         uint32_t pk[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          const float p0 = exp2f(fmaf(__uint_as_float(s[c * 8 + 2 * i]), scale_log2e, -m_run));
-          const float p1 = exp2f(fmaf(__uint_as_float(s[c * 8 + 2 * i + 1]), scale_log2e, -m_run));
-          l_blk += p0 + p1;
+          float x0, x1;
+          unpack_f32x2(fma_f32x2(pack_f32x2(s[c * 8 + 2 * i], s[c * 8 + 2 * i + 1]), scale2, negm2), x0, x1);
+          const float p0 = ex2_approx(x0), p1 = ex2_approx(x1);
+          l2 = add_f32x2(l2, pack_f32x2(__float_as_uint(p0), __float_as_uint(p1)));
           pk[i] = pack_bf16(p0, p1);
         }
         *reinterpret_cast<uint4*>(p_row + (c >> 3) * kPfQHalf + (((c & 7) ^ sw) << 4)) =
             make_uint4(pk[0], pk[1], pk[2], pk[3]);
       }
-      l_run += l_blk;
+      float l_lo, l_hi;
+      unpack_f32x2(l2, l_lo, l_hi);
+      l_run += l_lo + l_hi;
       tc_fence_before();            // orders the O rescale (tcgen05.st) before the MMA warp's next PV
       fence_proxy_async();          // P stores -> visible to the tensor core's async proxy
       mbar_arrive(p_full);

@@ -95,6 +95,30 @@ def config_for(model_name: str) -> ModelConfig:
     raise KeyError(f"no architecture known for model {model_name!r}")
 
 
+def config_from_dir(model_dir: str) -> ModelConfig:
+    """ModelConfig from a local HuggingFace model directory's config.json (the file vLLM reads when
+    the reference names a model, vllm_agent.py:126-144).  Dense Qwen3 / Qwen2 / Llama / Mistral-style
+    decoders with head_dim 128 are what the kernels support."""
+    import json
+    from pathlib import Path
+    c = json.loads((Path(model_dir) / "config.json").read_text())
+    mt = str(c.get("model_type", "")).lower()
+    heads = int(c["num_attention_heads"])
+    head_dim = int(c.get("head_dim") or c["hidden_size"] // heads)
+    if head_dim != 128:
+        raise ValueError(f"{model_dir}: head_dim {head_dim} is not supported (the attention kernels are built for 128)")
+    if c.get("num_local_experts") or c.get("num_experts"):
+        raise ValueError(f"{model_dir}: mixture-of-experts models are not supported")
+    theta = c.get("rope_theta") or (c.get("rope_parameters") or {}).get("rope_theta") or 1e6
+    return ModelConfig(name=Path(model_dir).name, n_layers=int(c["num_hidden_layers"]), d_model=int(c["hidden_size"]),
+                       n_heads=heads, n_kv_heads=int(c.get("num_key_value_heads") or heads),
+                       d_ff=int(c["intermediate_size"]), vocab=int(c["vocab_size"]), head_dim=head_dim,
+                       rms_eps=float(c.get("rms_norm_eps", 1e-6)), rope_theta=float(theta),
+                       qk_norm=mt.startswith("qwen3"), tie_embeddings=bool(c.get("tie_word_embeddings", False)),
+                       family="mistral" if ("mistral" in mt or "llama" in mt) else "qwen3",
+                       max_pos=min(int(c.get("max_position_embeddings", 8192)), 32768))
+
+
 def rope_table(cfg: ModelConfig, device) -> torch.Tensor:
     """[max_pos, 128] fp32: cos(pos * inv_freq)[0:64] | sin(...)[0:64], computed as transformers
     does (modeling_qwen3.py Qwen3RotaryEmbedding: inv_freq fp32, outer product fp32)."""
@@ -203,20 +227,68 @@ class Weights:
         lm = embed if cfg.tie_embeddings or "lm_head.weight" not in sd else bf(sd["lm_head.weight"])
         w = Weights(cfg, embed, lm, f32(sd["model.norm.weight"]))
         for l in range(cfg.n_layers):
-            p = f"model.layers.{l}."
-            w.ln1.append(f32(sd[p + "input_layernorm.weight"]))
-            w.ln2.append(f32(sd[p + "post_attention_layernorm.weight"]))
-            w.w_qkv.append(bf(torch.cat([sd[p + "self_attn.q_proj.weight"],
-                                         sd[p + "self_attn.k_proj.weight"],
-                                         sd[p + "self_attn.v_proj.weight"]], dim=0)))
-            w.w_o.append(bf(sd[p + "self_attn.o_proj.weight"]))
-            w.w_gate_up.append(bf(interleave_gate_up(sd[p + "mlp.gate_proj.weight"],
-                                                     sd[p + "mlp.up_proj.weight"])))
-            w.w_down.append(bf(sd[p + "mlp.down_proj.weight"]))
-            if cfg.qk_norm:
-                w.q_norm.append(f32(sd[p + "self_attn.q_norm.weight"]))
-                w.k_norm.append(f32(sd[p + "self_attn.k_norm.weight"]))
+            w._append_layer(sd, f"model.layers.{l}.", device)
         w.cos_sin = rope_table(cfg, device)
+        return w
+
+    def _append_layer(self, sd, p: str, device) -> None:
+        """Pack one decoder layer's transformers-named tensors (prefix p) into the engine's layout."""
+        def bf(t):
+            return t.detach().to(torch.bfloat16).contiguous().to(device)
+
+        def f32(t):
+            return t.detach().float().contiguous().to(device)
+
+        self.ln1.append(f32(sd[p + "input_layernorm.weight"]))
+        self.ln2.append(f32(sd[p + "post_attention_layernorm.weight"]))
+        self.w_qkv.append(bf(torch.cat([sd[p + "self_attn.q_proj.weight"],
+                                        sd[p + "self_attn.k_proj.weight"],
+                                        sd[p + "self_attn.v_proj.weight"]], dim=0)))
+        self.w_o.append(bf(sd[p + "self_attn.o_proj.weight"]))
+        self.w_gate_up.append(bf(interleave_gate_up(sd[p + "mlp.gate_proj.weight"],
+                                                    sd[p + "mlp.up_proj.weight"])))
+        self.w_down.append(bf(sd[p + "mlp.down_proj.weight"]))
+        if self.cfg.qk_norm:
+            self.q_norm.append(f32(sd[p + "self_attn.q_norm.weight"]))
+            self.k_norm.append(f32(sd[p + "self_attn.k_norm.weight"]))
+
+    @staticmethod
+    def from_safetensors_dir(cfg: ModelConfig, model_dir: str, device) -> "Weights":
+        """Checkpoint of a local HuggingFace model directory (model.safetensors, or the shards listed in
+        model.safetensors.index.json), read tensor by tensor and packed exactly as from_hf_state_dict
+        packs a state dict — never more than one decoder layer in host memory."""
+        import json
+        from pathlib import Path
+
+        from safetensors import safe_open
+        d = Path(model_dir)
+        index = d / "model.safetensors.index.json"
+        if index.exists():
+            where = json.loads(index.read_text())["weight_map"]
+        else:
+            with safe_open(str(d / "model.safetensors"), "pt") as f:
+                where = {k: "model.safetensors" for k in f.keys()}
+        handles = {}
+
+        def get(name):
+            fn = where[name]
+            if fn not in handles:
+                handles[fn] = safe_open(str(d / fn), "pt")
+            return handles[fn].get_tensor(name)
+
+        class Lazy(dict):
+            def __missing__(self, key):
+                return get(key)
+
+            def __contains__(self, key):
+                return key in where
+
+        # top-level tensors, then one layer at a time through the same packing code
+        sd = Lazy()
+        w = Weights.from_hf_state_dict(ModelConfig(**{**cfg.__dict__, "n_layers": 0}), sd, device)
+        w.cfg = cfg
+        for l in range(cfg.n_layers):
+            w._append_layer(sd, f"model.layers.{l}.", device)
         return w
 
     def shard(self, rank: int, size: int) -> "Weights":

@@ -251,3 +251,60 @@ class SyntheticTokenizer:
 @lru_cache(maxsize=8)
 def get_tokenizer(family: str = "qwen3", vocab_size: int = 151936) -> SyntheticTokenizer:
     return SyntheticTokenizer(family, vocab_size)
+
+
+class LocalTokenizer(SyntheticTokenizer):
+    """A real HuggingFace `tokenizer.json` from a local model directory (what the reference lets vLLM
+    load by name, vllm_agent.py:126-144) behind the same interface as the synthetic tokenizer:
+    encode / decode plus the id -> bytes table the grammar compiler and the sampler kernel need.
+    Handles byte-level BPE vocabularies (Qwen: GPT-2 byte alphabet) and SentencePiece-style ones
+    with byte fallback (Mistral: "▁" for blanks, <0xNN> byte tokens)."""
+
+    def __init__(self, model_dir: str, vocab_size: int, family: str = "qwen3"):  # noqa: super().__init__ not wanted
+        from tokenizers import Tokenizer
+        d = Path(model_dir)
+        self.family, self.vocab_size = family, vocab_size
+        self._tok = Tokenizer.from_file(str(d / "tokenizer.json"))
+        spec = json.loads((d / "tokenizer.json").read_text())
+        byte_level = "ByteLevel" in json.dumps(spec.get("pre_tokenizer") or {}) + json.dumps(spec.get("decoder") or {})
+        added = {a["id"]: a for a in spec.get("added_tokens", [])}
+        self.special_ids = {a["content"]: i for i, a in added.items() if a.get("special", True)}
+        self.token_bytes = [b""] * vocab_size
+        for tok_str, i in self._tok.get_vocab(with_added_tokens=True).items():
+            if i >= vocab_size or i in added:
+                continue
+            if byte_level:
+                try:
+                    self.token_bytes[i] = bytes(_U2B[c] for c in tok_str)
+                except KeyError:
+                    self.token_bytes[i] = tok_str.encode("utf-8")
+            elif len(tok_str) == 6 and tok_str.startswith("<0x") and tok_str.endswith(">"):
+                self.token_bytes[i] = bytes([int(tok_str[3:5], 16)])
+            else:
+                self.token_bytes[i] = tok_str.replace("▁", " ").encode("utf-8")
+        cfg = {}
+        for name in ("generation_config.json", "config.json", "tokenizer_config.json"):
+            if (d / name).exists():
+                for k, v in json.loads((d / name).read_text()).items():
+                    cfg.setdefault(k, v)
+
+        def token_id(v):
+            if isinstance(v, dict):
+                v = v.get("content")
+            return self._tok.token_to_id(v) if isinstance(v, str) else v
+
+        eos = cfg.get("eos_token_id", cfg.get("eos_token"))
+        eos = [token_id(e) for e in (eos if isinstance(eos, list) else [eos]) if e is not None]
+        if family != "mistral":   # ChatML turns end with <|im_end|> (vLLM takes it from generation_config)
+            eos += [i for s, i in self.special_ids.items() if s in ("<|im_end|>", "<|endoftext|>")]
+        self.stop_ids = tuple(dict.fromkeys(int(e) for e in eos if e is not None))[:2]
+        if not self.stop_ids:
+            raise ValueError(f"no end-of-sequence token found in {model_dir}")
+        self.eos_id = self.stop_ids[0]
+        add_bos = bool(cfg.get("add_bos_token", family == "mistral"))
+        self.bos_id = token_id(cfg.get("bos_token_id", cfg.get("bos_token"))) if add_bos else None
+        regular = [i for i in range(vocab_size) if self.token_bytes[i]]
+        self.n_regular = len(regular)
+        self.regular_range = (min(regular), max(regular) + 1)
+        self._is_special = np.zeros(vocab_size, bool)
+        self._is_special[[i for i in self.special_ids.values() if i < vocab_size]] = True

@@ -90,15 +90,24 @@ class B200LLM:
             self.cfg, self.tokenizer, self.engine = self.tp.cfg, self.tp.tokenizer, self.tp.engine
             return
         key = model_name.lower()
+        tokenizer = None
         if key in _REGISTRY:
             cfg, factory = _REGISTRY[key]
+        elif os.path.isdir(model_name) and os.path.exists(os.path.join(model_name, "config.json")):
+            # a local HuggingFace model directory: its own architecture, checkpoint and tokenizer —
+            # what the reference gets when vLLM resolves the model name (vllm_agent.py:126-144)
+            from .tokenizer import LocalTokenizer
+            cfg = M.config_from_dir(model_name)
+            factory = lambda c, dev: M.Weights.from_safetensors_dir(c, model_name, dev)
+            if os.path.exists(os.path.join(model_name, "tokenizer.json")):
+                tokenizer = LocalTokenizer(model_name, cfg.vocab, cfg.family)
         else:
             cfg = M.config_for(model_name)
             seed = int(model_config.get("weight_seed", os.environ.get("BCG_B200_WEIGHT_SEED", 0)))
             factory = lambda c, dev: M.Weights.random_init(c, dev, seed=seed)
         device = model_config.get("device", "cuda:0")
         self.cfg = cfg
-        self.tokenizer = get_tokenizer(cfg.family, cfg.vocab)
+        self.tokenizer = tokenizer or get_tokenizer(cfg.family, cfg.vocab)
         weights = factory(cfg, torch.device(device))
         self.engine = Engine(
             cfg, weights, self.tokenizer,
