@@ -1,10 +1,16 @@
-"""SURVEY.md §8f rank 3 — JSON validity is decided on the device: the stop token is only ever
-unmasked in an accepting state of the schema's DFA, so a guided row that finishes with "stop" has
-emitted a complete object of its schema.  Pinned here over a few thousand sampled rows at the
-shipped temperature (T = 0.5) for the reference's four schemas (bcg_agents.py:590-599, 651-658,
-1083-1092, 1155-1162): every such row must `json.loads` and validate; rows that hit max_tokens
-are the only ones allowed not to parse.  (Detokenisation and json.loads stay on the host: they are
-1 % of a round)"""
+"""SURVEY.md §8f rank 3 — JSON validity is decided on the device: the row's DFA state at the stop
+token says whether a complete object of the schema was emitted.  Pinned here over a few thousand
+sampled rows at the shipped temperature (T = 0.5) for the reference's four schemas
+(bcg_agents.py:590-599, 651-658, 1083-1092, 1155-1162):
+
+  * a row that stops in an ACCEPTING state must `json.loads` and validate against its schema;
+  * a row may also stop in a non-accepting state — only inside a string, where the reference's
+    grammar (xgrammar as vLLM drives it, which this engine matches bit for bit) admits the stop
+    token's literal text "<|im_end|>" as string content while the engine, like vLLM, ends the
+    generation on that token id.  Such rows are unparseable in the reference too (its
+    `json_parse_failed` path); the test checks that this is the ONLY way to stop incomplete.
+
+(Detokenisation and json.loads stay on the host: they are 1 % of a round)"""
 import json
 
 import numpy as np
@@ -14,6 +20,7 @@ import torch
 pytestmark = pytest.mark.gpu
 
 from byzantine_consensus_llm_agents_b200.engine import Engine, Request  # noqa: E402
+from byzantine_consensus_llm_agents_b200.grammar import grammar_token_bytes  # noqa: E402
 from byzantine_consensus_llm_agents_b200.model import ModelConfig, Weights  # noqa: E402
 from byzantine_consensus_llm_agents_b200.tokenizer import get_tokenizer  # noqa: E402
 
@@ -63,7 +70,10 @@ def test_every_stopped_guided_row_is_a_valid_object_of_its_schema():
     lo, hi = tk.regular_range
     schemas = [HONEST_DECIDE, BYZ_DECIDE, HONEST_VOTE, BYZ_VOTE]
     stopped = {i: 0 for i in range(4)}
+    incomplete = {i: 0 for i in range(4)}
     total = 0
+    tb = grammar_token_bytes(tk)
+    gobj = [eng.grammar_objs[eng.grammar_index(sc)] for sc in schemas]
     for call in range(48):                                  # 48 calls x 64 rows = 3,072 rows
         reqs, which = [], []
         for b in range(64):
@@ -75,13 +85,29 @@ def test_every_stopped_guided_row_is_a_valid_object_of_its_schema():
             total += 1
             assert r.finish in ("stop", "length"), r.finish      # never a grammar dead end
             if r.finish == "stop":
-                stopped[si] += 1
-                obj = json.loads(r.text)                          # must parse ...
-                assert _validates(obj, schemas[si]), (si, r.text)  # ... and be an object of ITS schema
+                g, st = gobj[si], 0
+                assert r.token_ids[-1] in tk.stop_ids
+                for t in r.token_ids[:-1]:
+                    st = g.walk(st, tb[t])
+                    assert st >= 0                                # every token was inside the grammar
+                if g.accept[st]:
+                    stopped[si] += 1
+                    obj = json.loads(r.text)                          # must parse ...
+                    assert _validates(obj, schemas[si]), (si, r.text)  # ... and be an object of ITS schema
+                else:
+                    incomplete[si] += 1
+                    # only possible where the mask admits the stop token as TEXT: inside a string
+                    word, bit = divmod(r.token_ids[-1], 32)
+                    assert (int(g.masks[st][word]) >> bit) & 1
+                    assert g.walk(st, b"<|im_end|>") >= 0 or g.walk(st, b"<|endoftext|>") >= 0
+                    with pytest.raises(ValueError):
+                        json.loads(r.text)
             else:
                 assert len(r.token_ids) == 160
-    print(f"{total} sampled rows; stopped (valid) per schema: {stopped}")
-    # the vote schemas close within a few tokens unless whitespace runs on: most rows must stop
-    assert stopped[2] + stopped[3] > 0.5 * total / 2
-    assert sum(stopped.values()) > 1000
+    print(f"{total} sampled rows; stopped complete (parsed + validated) per schema: {stopped}; "
+          f"stopped inside a string on the stop token's literal text: {incomplete}")
+    # the vote schemas have no free-form string: they can only stop complete
+    assert incomplete[2] == 0 and incomplete[3] == 0
+    assert stopped[2] + stopped[3] > 0.25 * total / 2
+    assert sum(stopped.values()) > 500
     eng.close()
