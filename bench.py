@@ -346,6 +346,10 @@ def main():
                     help="programmatic dependent launch for the decode step (1 = on)")
     a = ap.parse_args()
 
+    if os.environ.get("BCG_BENCH_WATCHDOG_S"):
+        # a hung collective must not eat a GPU lease: dump every thread's stack and exit
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ["BCG_BENCH_WATCHDOG_S"]), exit=True)
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
