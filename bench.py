@@ -391,9 +391,13 @@ def main():
 
     import torch
     import torch.distributed as dist
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
     torch.cuda.set_device(local_rank)
+    if world > 1:
+        # No device_id when tensor-parallel replicas are cut out of the world: with an eagerly bound
+        # NCCL communicator torch makes every NON-member of a later new_group() take part in an
+        # ncclCommSplit that the members of a gloo group never join (a hang).
+        kw = {} if a.tp > 1 else {"device_id": torch.device(f"cuda:{local_rank}")}
+        dist.init_process_group("nccl", **kw)
 
     from byzantine_consensus_llm_agents_b200 import vllm_agent as VA
     model_name = HF_NAME.get(a.model, a.model)

@@ -172,7 +172,7 @@ int bcg_tp_init(const void* id_128_bytes, int rank, int size) { return tp_init(i
 int bcg_tp_shutdown(void) { return tp_shutdown(); }
 long long bcg_tp_symm_bytes_for(long long region_floats, int size) {
   if (region_floats < 0 || size < 1) return 0;
-  return 4 * (tp_symm_flag_floats() + 2 * static_cast<long long>(size) * region_floats);
+  return 4 * (tp_symm_flag_floats() + 4 * static_cast<long long>(size) * region_floats);
 }
 int bcg_tp_add_norm_stats(float* residual, const float* partials, int n_partials, long long partial_stride,
                           const float* w, void* xn, float* sumsq, int slot, long long region_floats, int T,

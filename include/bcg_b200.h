@@ -258,12 +258,13 @@ int bcg_tp_shutdown(void);
 /* The symmetric buffer every rank of the replica maps (cudaIpc over NVLink).  It carries the
  * sampler's per-row candidate exchange (bcg_sampler_args.tp_size > 1) and, when
  * bcg_workspace.tp_region_floats > 0, the decode step's two per-layer all-reduces, fused into the
- * norm-statistics kernel that follows each row-parallel projection (bcg_tp_add_norm_stats: pushes
- * over NVLink + flags, no NCCL launch); with tp_region_floats == 0 the decode step all-reduces with
+ * norm-statistics kernel that follows each row-parallel projection (bcg_tp_add_norm_stats: {value,
+ * epoch} pushes over NVLink, no flag, no fence, no NCCL launch); with tp_region_floats == 0 the decode step all-reduces with
  * NCCL.  create: cudaMalloc's `bytes` (the only allocation this library ever makes; freed by
  * bcg_tp_shutdown) and returns the 64-byte IPC handle; open: takes all ranks' handles in rank
- * order.  bytes = bcg_tp_symm_bytes_for(region, size) = 4 * (32768 + 2 * size * region) with
- * region = tp_region_floats >= B_max * d_model (0 if only the sampler uses the buffer). */
+ * order.  bytes = bcg_tp_symm_bytes_for(region, size) = 4 * (32768 + 4 * size * region) with
+ * region = tp_region_floats >= B_max * d_model (0 if only the sampler uses the buffer): two slots,
+ * one inbox per source rank, every value stored beside the launch's epoch. */
 long long bcg_tp_symm_bytes_for(long long region_floats, int size);
 int bcg_tp_symm_create(long long bytes, void* handle_out_64_bytes /* host */);
 int bcg_tp_symm_open(const void* handles_size_x_64_bytes /* host */, int rank, int size);
