@@ -321,12 +321,11 @@ class VLLMAgent:
         except Exception as e:
             if VERBOSE:
                 print(f"Warning: CUDA cleanup failed: {e}", flush=True)
-        try:
-            import torch.distributed as dist
-            if dist.is_available() and dist.is_initialized():
-                dist.destroy_process_group()
-        except Exception:
-            pass
+        # The reference also tears down torch.distributed here (vllm_agent.py:540-547) because vLLM's
+        # `mp` executor had created the groups.  The counterpart of that — the control group of a
+        # spawned tensor-parallel replica — is destroyed by SpawnedTP.close() above; a process group
+        # the CALLER created (torchrun: data-parallel replicas, tensor-parallel replicas cut out of
+        # the world) is the caller's to destroy, other ranks may still be waiting on it.
         gc.collect()
         if VERBOSE:
             print("✓ B200 engine shutdown complete", flush=True)
