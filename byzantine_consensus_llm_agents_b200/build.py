@@ -23,6 +23,7 @@ LIB_TIMELINE = OUT / "libbcg_b200_tl.so"
 SOURCES = [
     "capi.cu",
     "gemm_tcgen05.cu",
+    "gemm2sm_tcgen05.cu",
     "norm_rope.cu",
     "attn_decode.cu",
     "attn_prefill.cu",

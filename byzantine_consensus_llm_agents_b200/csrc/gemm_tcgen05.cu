@@ -570,6 +570,11 @@ int gemm_bf16_tn_fused(const void* X, const void* W, void* out, int M, int N, in
     set_last_error("bcg_gemm_bf16_tn", "ld_out must keep 16-byte row alignment");
     return BCG_ERR_ARG;
   }
+  if (!swap && splits == 1 && !(fu && (fu->scale_sumsq || fu->red_counters))) {
+    // prefill-sized: 256x256 tiles on CTA pairs when the shape allows it
+    const int rc2 = gemm2sm_bf16_tn(X, W, out, M, N, K, ldx, ldw, ld_out, epi, stream);
+    if (rc2 != BCG_ERR_UNSUPPORTED) return rc2;
+  }
   GemmArgs a = {};
   a.M = M;
   a.N = N;

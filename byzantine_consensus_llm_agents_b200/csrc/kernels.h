@@ -16,6 +16,9 @@ int gemm_bf16_tn_fused(const void* X, const void* W, void* out, int M, int N, in
                        long long ldw, long long ld_out, int epi, int splits, int flags,
                        const bcg_gemm_fusion* fusion, cudaStream_t stream);
 int gemm_splits_for(int M, int N, int K);
+// Prefill shapes on CTA pairs (tcgen05.mma.cta_group::2); BCG_ERR_UNSUPPORTED = not a shape for it
+int gemm2sm_bf16_tn(const void* X, const void* W, void* out, int M, int N, int K, long long ldx, long long ldw,
+                    long long ld_out, int epi, cudaStream_t stream);
 // TMA descriptor of a row-major bf16 matrix (rows x K, pitch ld elements): boxes of box_rows x 64
 // elements land in shared memory 128B-swizzled, out-of-bounds elements read as zero.
 int make_tmap_bf16_sw128(CUtensorMap* m, const void* ptr, long long rows, long long K, long long ld,

@@ -42,6 +42,12 @@ GEMM_SHAPES = [
     (300, 512, 256),
     (1000, 1024, 512),
     (4096, 2048, 1024),
+    # prefill shapes on CTA pairs (M >= 512, N % 256 == 0): one k-block, ragged K, ragged M inside the
+    # pair's second CTA, more tiles than clusters (several tiles per cluster, both accumulator stages)
+    (513, 256, 64),
+    (700, 768, 320),
+    (641, 512, 4096),
+    (4096, 7168, 512),
 ]
 
 
