@@ -7,11 +7,14 @@
 // of the B tile (128 of its 256 weight rows), the leader CTA issues one M=256 MMA that reads both
 // halves, and every CTA's accumulator (its 128 rows x 256 columns) stays in its own TMEM.  Per CTA and
 // k-block that is 32 KB of operands for the same tensor work: 64 B per clock.
+// Measured on a layer's four projections at 12,390 tokens (tools/prefill_gemm_time.py): 1,285 TFLOP/s
+// single-CTA -> 1,317 (6 stages, raster groups of 8 m-tiles) -> 1,357 (groups of 12) -> 1,367 (7 stages);
+// cuBLAS on the same shapes averages ~1,480.
 //
 //   cluster (2,1,1), 192 threads per CTA, persistent over 256x256 tiles.
 //   warp 0   TMA producer in BOTH CTAs: its A rows and its half of B (tensor maps over this GPU's
 //            buffers; `.cta_group::2` loads whose completion bytes land on the LEADER's full barrier —
-//            no multicast), ring of 6 x 32 KB stages; slots are freed by the leader's MMA commits,
+//            no multicast), ring of 7 x 32 KB stages; slots are freed by the leader's MMA commits,
 //            multicast to both CTAs' empty barriers.
 //   warp 1   leader CTA: MMA issuer (4 x tcgen05.mma.cta_group::2 m256 n256 k16 per k-block), two
 //            accumulator stages of 256 TMEM columns; both CTAs: TMEM alloc / dealloc (cta_group::2).
@@ -28,12 +31,11 @@ namespace bcg {
 constexpr int k2BlockM = 128;       // rows of A per CTA (256 per pair)
 constexpr int k2BlockN = 256;       // output columns per tile; each CTA stages 128 of the B rows
 constexpr int k2BlockK = 64;
-constexpr int k2Stages = 6;
 constexpr int k2Threads = 192;
 constexpr int k2ABytes = k2BlockM * k2BlockK * 2;          // 16 KB
 constexpr int k2BBytes = (k2BlockN / 2) * k2BlockK * 2;    // 16 KB
 constexpr int k2StageBytes = k2ABytes + k2BBytes;
-constexpr int k2Smem = k2Stages * k2StageBytes + 1024 + 256;
+constexpr int smem_2sm(int stages) { return stages * k2StageBytes + 1024 + 256; }
 constexpr uint32_t k2TmemCols = 512;
 // kind::f16, D = f32, A = B = bf16, both K-major, M = 256 (pair), N = 256
 constexpr uint32_t k2Idesc = (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(k2BlockN >> 3) << 17) |
@@ -110,6 +112,7 @@ __device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
 
 __device__ __forceinline__ float silu_mul2(float g, float u) { return g * (1.0f / (1.0f + __expf(-g))) * u; }
 
+template <int k2Stages>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1)
 gemm2sm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                        const Gemm2Args args) {
@@ -324,7 +327,9 @@ int gemm2sm_bf16_tn(const void* X, const void* W, void* out, int M, int N, int K
   a.tiles_m = (M + 255) / 256;
   a.tiles_n = N / k2BlockN;
   a.k_blocks = (K + k2BlockK - 1) / k2BlockK;
-  a.group_m = a.tiles_m < 8 ? a.tiles_m : 8;
+  static const int group = getenv("BCG_GEMM_2SM_GROUP") ? atoi(getenv("BCG_GEMM_2SM_GROUP")) : 12;   // tuning knobs
+  static const int stages = getenv("BCG_GEMM_2SM_STAGES") ? atoi(getenv("BCG_GEMM_2SM_STAGES")) : 7;
+  a.group_m = a.tiles_m < group ? a.tiles_m : group;
   a.epi = epi;
   a.out = out;
   a.ld_out = ld_out;
@@ -332,14 +337,22 @@ int gemm2sm_bf16_tn(const void* X, const void* W, void* out, int M, int N, int K
   int rc;
   if ((rc = make_tmap_bf16_sw128(&tma, X, M, K, ldx, k2BlockM)) != BCG_OK) return rc;
   if ((rc = make_tmap_bf16_sw128(&tmb, W, N, K, ldw, k2BlockN / 2)) != BCG_OK) return rc;
-  if ((rc = ensure_dynamic_smem(reinterpret_cast<const void*>(gemm2sm_tcgen05_kernel), k2Smem))) return rc;
+
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   int clusters = sms / 2;
   const int total = a.tiles_m * a.tiles_n;
   if (clusters > total) clusters = total;
-  BCG_CUDA_CHECK(launch_k(gemm2sm_tcgen05_kernel, dim3(2 * clusters), dim3(k2Threads), k2Smem, stream, tma, tmb, a));
+  if (stages != 6) {
+    if ((rc = ensure_dynamic_smem(reinterpret_cast<const void*>(gemm2sm_tcgen05_kernel<7>), smem_2sm(7)))) return rc;
+    BCG_CUDA_CHECK(launch_k(gemm2sm_tcgen05_kernel<7>, dim3(2 * clusters), dim3(k2Threads), smem_2sm(7), stream, tma,
+                            tmb, a));
+  } else {
+    if ((rc = ensure_dynamic_smem(reinterpret_cast<const void*>(gemm2sm_tcgen05_kernel<6>), smem_2sm(6)))) return rc;
+    BCG_CUDA_CHECK(launch_k(gemm2sm_tcgen05_kernel<6>, dim3(2 * clusters), dim3(k2Threads), smem_2sm(6), stream, tma,
+                            tmb, a));
+  }
   return BCG_OK;
 }
 

@@ -10,6 +10,7 @@
 // Arithmetic follows transformers' Qwen3RMSNorm / apply_rotary_pos_emb in fp32
 // (modeling_qwen3.py:50-64,86-148 as cited in SURVEY.md §8c).
 #include <cooperative_groups.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "kernels.h"
@@ -444,6 +445,88 @@ qknorm_rope_kvwrite_kernel(const void* __restrict__ qkv, int qkv_is_f32, int n_p
   }
 }
 
+// Prefill-sized launches (one fp32 slab, thousands of tokens): the kernel above starts a 4-warp CTA per
+// four (token, head) pairs — 173,460 CTAs of ~1.5 us at 12.4k tokens, each lane with 16 bytes of
+// loads in flight: 2.25 TB/s, a third of the HBM rate (ncu, profiles/r02_prof_prefill_glue_raw.csv).
+// Here one CTA owns a TOKEN: position, cache slot, RoPE row and norm weights are fetched once per
+// warp, warp w takes heads w, w+8, ... and keeps four heads' loads in flight before it touches any.
+// Per head the lane mapping and every arithmetic step are those of the kernel above, so a row's
+// q / k / v bits do not depend on which of the two kernels produced them (decode uses the other one).
+constexpr int kRopeTokWarps = 8;
+constexpr int kRopeTokBatch = 4;
+
+__global__ void __launch_bounds__(kRopeTokWarps * 32)
+qknorm_rope_kvwrite_token_kernel(const float* __restrict__ qkv, long long ld_qkv,
+                                 const float* __restrict__ q_norm_w, const float* __restrict__ k_norm_w,
+                                 const float* __restrict__ cos_sin, const int* __restrict__ positions,
+                                 const int* __restrict__ slot_map, __nv_bfloat16* __restrict__ q_out,
+                                 __nv_bfloat16* __restrict__ kv_cache, int n_heads, int n_kv_heads,
+                                 int page_size, float eps) {
+  pdl_launch_dependents();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int t = blockIdx.x;
+  const int heads_total = n_heads + 2 * n_kv_heads;
+  const int pos = positions[t];
+  const int slot = slot_map[t];
+  const float2 c = *reinterpret_cast<const float2*>(cos_sin + static_cast<long long>(pos) * 128 + 2 * lane);
+  const float2 sn = *reinterpret_cast<const float2*>(cos_sin + static_cast<long long>(pos) * 128 + 64 + 2 * lane);
+  float2 qwl = make_float2(1.f, 1.f), qwh = qwl, kwl = qwl, kwh = qwl;
+  if (q_norm_w) {
+    qwl = *reinterpret_cast<const float2*>(q_norm_w + 2 * lane);
+    qwh = *reinterpret_cast<const float2*>(q_norm_w + 64 + 2 * lane);
+  }
+  if (k_norm_w) {
+    kwl = *reinterpret_cast<const float2*>(k_norm_w + 2 * lane);
+    kwh = *reinterpret_cast<const float2*>(k_norm_w + 64 + 2 * lane);
+  }
+  pdl_wait();
+  const float* row = qkv + static_cast<long long>(t) * ld_qkv;
+  for (int h0 = warp; h0 < heads_total; h0 += kRopeTokWarps * kRopeTokBatch) {
+    float2 a[kRopeTokBatch], b[kRopeTokBatch];
+#pragma unroll
+    for (int i = 0; i < kRopeTokBatch; ++i) {      // clamped: all loads of the batch in flight at once
+      const int h = min(h0 + i * kRopeTokWarps, heads_total - 1);
+      a[i] = *reinterpret_cast<const float2*>(row + h * 128 + 2 * lane);
+      b[i] = *reinterpret_cast<const float2*>(row + h * 128 + 64 + 2 * lane);
+    }
+#pragma unroll
+    for (int i = 0; i < kRopeTokBatch; ++i) {
+      const int h = h0 + i * kRopeTokWarps;
+      if (h >= heads_total) break;
+      const bool is_q = h < n_heads;
+      const bool is_k = !is_q && h < n_heads + n_kv_heads;
+      float lo0 = a[i].x, lo1 = a[i].y, hi0 = b[i].x, hi1 = b[i].y;
+      if (is_q || is_k) {
+        if (is_q ? (q_norm_w != nullptr) : (k_norm_w != nullptr)) {
+          const float2 wl = is_q ? qwl : kwl, wh = is_q ? qwh : kwh;
+          const float ss = warp_sum(lo0 * lo0 + lo1 * lo1 + hi0 * hi0 + hi1 * hi1);
+          const float inv = rsqrtf(ss * (1.0f / 128.0f) + eps);
+          lo0 = lo0 * inv * wl.x; lo1 = lo1 * inv * wl.y;
+          hi0 = hi0 * inv * wh.x; hi1 = hi1 * inv * wh.y;
+        }
+        const float r_lo0 = lo0 * c.x - hi0 * sn.x;
+        const float r_lo1 = lo1 * c.y - hi1 * sn.y;
+        const float r_hi0 = hi0 * c.x + lo0 * sn.x;
+        const float r_hi1 = hi1 * c.y + lo1 * sn.y;
+        lo0 = r_lo0; lo1 = r_lo1; hi0 = r_hi0; hi1 = r_hi1;
+      }
+      const uint32_t plo = pack_bf16(lo0, lo1), phi = pack_bf16(hi0, hi1);
+      if (is_q) {
+        __nv_bfloat16* o = q_out + (static_cast<long long>(t) * n_heads + h) * 128;
+        *reinterpret_cast<uint32_t*>(o + 2 * lane) = plo;
+        *reinterpret_cast<uint32_t*>(o + 64 + 2 * lane) = phi;
+      } else if (slot >= 0) {
+        const int kvh = is_k ? h - n_heads : h - n_heads - n_kv_heads;
+        const int page = slot / page_size, off = slot - page * page_size;
+        __nv_bfloat16* o = kv_cache +
+            (((static_cast<long long>(page) * 2 + (is_k ? 0 : 1)) * n_kv_heads + kvh) * page_size + off) * 128;
+        *reinterpret_cast<uint32_t*>(o + 2 * lane) = plo;
+        *reinterpret_cast<uint32_t*>(o + 64 + 2 * lane) = phi;
+      }
+    }
+  }
+}
+
 // act[t, f] = silu(gate) * up where the GEMM's N axis is interleaved [16 gate | 16 up].
 __global__ void __launch_bounds__(256)
 swiglu_reduce_kernel(const float* __restrict__ partials, int n_partials, long long partial_stride,
@@ -541,6 +624,16 @@ int qknorm_rope_kvwrite(const void* qkv, int qkv_is_f32, int n_partials, long lo
       n_heads <= 0 || n_kv_heads <= 0 || page_size <= 0 || n_partials < 1) {
     set_last_error("bcg_qknorm_rope_kvwrite", "bad argument");
     return BCG_ERR_ARG;
+  }
+  if (qkv_is_f32 && n_partials == 1 && T > 128) {   // prefill-sized: one CTA per token
+    static const bool off = getenv("BCG_ROPE_TOKEN_KERNEL") && atoi(getenv("BCG_ROPE_TOKEN_KERNEL")) == 0;
+    if (!off) {
+      BCG_CUDA_CHECK(launch_k(qknorm_rope_kvwrite_token_kernel, dim3(T), dim3(kRopeTokWarps * 32), 0, stream,
+                              reinterpret_cast<const float*>(qkv), ld_qkv, q_norm_w, k_norm_w, cos_sin, positions,
+                              slot_map, reinterpret_cast<__nv_bfloat16*>(q_out),
+                              reinterpret_cast<__nv_bfloat16*>(kv_cache), n_heads, n_kv_heads, page_size, eps));
+      return BCG_OK;
+    }
   }
   const long long warps = static_cast<long long>(T) * (n_heads + 2 * n_kv_heads);
   const unsigned grid = static_cast<unsigned>((warps + 3) / 4);

@@ -407,11 +407,14 @@ def _make_cos_sin(max_pos=4096, theta=1e6):
 
 
 @pytest.mark.parametrize("T,H,HKV,parts,qknorm", [(10, 4, 2, 0, True), (10, 40, 8, 3, True),
-                                                   (70, 16, 8, 0, True), (5, 6, 1, 2, False)])
+                                                   (70, 16, 8, 0, True), (5, 6, 1, 2, False),
+                                                   # prefill-sized fp32 slab: the token-per-CTA kernel
+                                                   (300, 40, 8, 1, True), (700, 64, 8, 1, True),
+                                                   (257, 48, 8, 1, False), (130, 3, 1, 1, True)])
 def test_qknorm_rope_kvwrite(T, H, HKV, parts, qknorm):
     lib = _lib()
     page = 16
-    n_pages = 64
+    n_pages = max(64, (T + 15) // 16 + 8)
     qkv_dim = (H + 2 * HKV) * 128
     cos_sin = _make_cos_sin()
     pos = torch.randint(0, 4000, (T,), device=DEV, dtype=torch.int32)
