@@ -342,6 +342,8 @@ def main():
                     help="tensor_parallel_size of each replica.  Plain `python bench.py --gpus T --tp T`: the "
                          "adapter spawns ranks 1..T-1 (like vLLM's mp executor).  Under torchrun with N ranks: "
                          "N/T replicas of T consecutive ranks each, one game per replica (TP composed with DP)")
+    ap.add_argument("--fused-rope", type=int, default=0,
+                    help="1: qk-norm / RoPE / KV write inside decode attention (one launch fewer per layer)")
     ap.add_argument("--pdl", type=int, default=int(os.environ.get("BCG_B200_PDL", "1")),
                     help="programmatic dependent launch for the decode step (1 = on)")
     a = ap.parse_args()
@@ -403,7 +405,8 @@ def main():
     model_name = HF_NAME.get(a.model, a.model)
     model_config = {"max_model_len": 8192, "gpu_memory_utilization": 0.9, "tensor_parallel_size": 1,
                     "max_num_seqs": 4, "disable_qwen3_thinking": True, "device": f"cuda:{local_rank}",
-                    "seed": 1000 + rank, "engine_max_rows": max(16, n_agents), "pdl": bool(a.pdl)}
+                    "seed": 1000 + rank, "engine_max_rows": max(16, n_agents), "pdl": bool(a.pdl),
+                    "fused_rope": bool(a.fused_rope)}
     # collectives of the measurement itself: the default NCCL group, or — when tensor-parallel
     # replicas are cut out of the torchrun world — a gloo group of the replica leaders
     leaders, lg, red_dev = world, None, "cuda"

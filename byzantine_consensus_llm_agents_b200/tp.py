@@ -134,6 +134,7 @@ def _build_engine(model_name: str, model_config: dict, rank: int, size: int):
                  base_seed=int(model_config.get("seed", os.environ.get("BCG_B200_SEED", 0))),
                  device=str(device), use_cuda_graph=bool(model_config.get("use_cuda_graph", True)),
                  pdl=bool(model_config.get("pdl", True)), tp_rank=rank, tp_size=size,
+                 fused_rope=bool(model_config.get("fused_rope", False)),
                  # decode all-reduces inside bcg_tp_add_norm_stats (pushes over NVLink) unless asked
                  # for NCCL
                  tp_fused_allreduce=bool(model_config.get("tp_fused_allreduce", True)),

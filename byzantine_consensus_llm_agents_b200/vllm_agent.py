@@ -118,7 +118,8 @@ class B200LLM:
             base_seed=int(model_config.get("seed", os.environ.get("BCG_B200_SEED", 0))),
             device=device,
             use_cuda_graph=bool(model_config.get("use_cuda_graph", True)),
-            pdl=bool(model_config.get("pdl", True)))
+            pdl=bool(model_config.get("pdl", True)),
+            fused_rope=bool(model_config.get("fused_rope", False)))
 
     def run(self, prompts: List[str], schemas: List[Optional[dict]], temperature: float,
             max_tokens: int) -> List[str]:
