@@ -27,7 +27,6 @@ SOURCES = [
     "norm_rope.cu",
     "attn_decode.cu",
     "attn_prefill.cu",
-    "attn_prefill_legacy.cu",
     "sampler.cu",
     "model_step.cu",
     "tp_comm.cu",

@@ -395,11 +395,6 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_cons
   if (warp == 1) tmem_dealloc(tmem_base, C::kTmemCols);
 }
 
-int prefill_attn_paged_legacy(const void* q, const void* kv_cache, const int* block_table,
-                              int max_blocks_per_seq, const int* tile_info, int n_tiles, void* out,
-                              int n_heads, int n_kv_heads, int page_size, float scale,
-                              cudaStream_t stream);
-
 int prefill_attn_paged(const void* q, const void* kv_cache, const int* block_table,
                        int max_blocks_per_seq, const int* tile_info, int n_tiles, void* out,
                        int n_q_rows, int n_heads, int n_kv_heads, int page_size, float scale,
@@ -418,10 +413,6 @@ int prefill_attn_paged(const void* q, const void* kv_cache, const int* block_tab
     set_last_error("bcg_prefill_attn_paged", "q, out and kv_cache must be 16-byte aligned");
     return BCG_ERR_ARG;
   }
-  static const bool legacy = getenv("BCG_PREFILL_ATTN_LEGACY") != nullptr;   // development only
-  if (legacy)
-    return prefill_attn_paged_legacy(q, kv_cache, block_table, max_blocks_per_seq, tile_info, n_tiles, out,
-                                     n_heads, n_kv_heads, page_size, scale, stream);
   // q as [n_q_rows, n_heads*128]: 128-row x 64-column boxes, rows past the end read as zero.
   // The cache as a [token-rows, 128] tensor: 16-row x 64-column boxes (one page of one KV head);
   // the row count only bounds TMA's range check, the block table never points past the allocation.

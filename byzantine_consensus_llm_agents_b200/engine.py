@@ -41,7 +41,7 @@ MAX_GRAMMARS = 64
 POLL_EVERY = 8      # tensor-parallel engines: steps between two synchronised looks at the active-row count
 IN_FLIGHT = 2       # single-GPU engines: decode steps queued ahead of the one whose result the host has seen
 # query rows per prefill-attention CTA (bcg_prefill_attn_paged)
-PREFILL_TILE = 64 if __import__("os").environ.get("BCG_PREFILL_ATTN_LEGACY") else 128
+PREFILL_TILE = 128
 
 
 def row_seed(base_seed: int, call_index: int, row: int):

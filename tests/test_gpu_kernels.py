@@ -673,7 +673,7 @@ def test_prefill_attn_paged_peaky_scores(H, HKV, spec):
 
 
 def _check_prefill_attn(H, HKV, spec, q_scale):
-    TILE = 64 if os.environ.get("BCG_PREFILL_ATTN_LEGACY") else 128
+    TILE = 128
     lib = _lib()
     G = H // HKV
     lens = [c + n for c, n in spec]

@@ -59,7 +59,7 @@ def run_case(lib, H, HKV, lens, cached=0, tile=128, reps=10):
 def main():
     import os
     lib = L.load()
-    tile = 64 if os.environ.get("BCG_PREFILL_ATTN_LEGACY") else 128
+    tile = 128
     out = []
     for H, HKV, lens, cached in ((40, 8, [1770] * 7, 0), (40, 8, [1296] * 10, 416), (40, 8, [4096] * 3, 0),
                                  (32, 8, [1770] * 8, 0), (48, 8, [1900] * 6, 0), (64, 8, [1770] * 4, 0)):
