@@ -65,6 +65,13 @@ def load_peaks():
     return 6650.0, 1590.0, "fallback"
 
 
+def load_sustained_tf():
+    """cuBLAS bf16 back to back for seconds (power-capped clocks) — the figure that applies to a GEMM
+    timed inside a long step; None when the driver has not measured it."""
+    p = ROOT / "MEASURED_PEAKS.json"
+    return json.loads(p.read_text()).get("bf16_tflops_sustained") if p.exists() else None
+
+
 def load_rounds(honest: int, byz: int, family: str = "qwen3"):
     p = ROOT / "tests" / "golden" / f"bench_prompts_{family}_{honest}h{byz}b.json.gz"
     with gzip.open(p, "rt") as f:
@@ -119,7 +126,7 @@ def agent_step(agent, rnd, counters):
               valid_vote, counters)
 
 
-def fixed_round(agent, engine, rnd):
+def fixed_round(agent, engine, rnd, acc=None):
     """One game round on the FIXED schedule: MAX_RETRIES batched attempts per phase, every row
     teacher-forced through "{" + blanks (valid in all four reference grammars, never accepting),
     so every call runs all its rows to max_tokens.  Returns the number of engine calls."""
@@ -134,7 +141,12 @@ def fixed_round(agent, engine, rnd):
         for _ in range(MAX_RETRIES):
             reqs = [Request(agent._format_chat_prompt(s, u), sc, temp, mt, forced=forced)
                     for s, u, sc in rnd[phase]["prompts"]]
+            s0 = dict(engine.stats)
             res = (agent.llm.tp.generate if agent.llm.tp is not None else engine.generate)(reqs)
+            if acc is not None:      # decode time per phase (the two phases differ in context length)
+                acc.setdefault(phase, [0.0, 0])
+                acc[phase][0] += engine.stats["decode_s"] - s0["decode_s"]
+                acc[phase][1] += engine.stats["decode_steps"] - s0["decode_steps"]
             short = [(len(r.token_ids), r.finish) for r in res if len(r.token_ids) != mt]
             if short:
                 raise RuntimeError(f"fixed schedule: {len(short)} of {len(res)} {phase} rows did not run to {mt} "
@@ -470,6 +482,7 @@ def main():
     # ---- the fixed schedule (identical work everywhere; see the module docstring)
     fixed = None
     fixed_error = None
+    fixed_phases = {}
     if a.fixed_rounds > 0:
         if a.tp == 1:
             engine.reset_prefix_cache()
@@ -480,7 +493,7 @@ def main():
             barrier()
             f0 = dict(engine.stats)
             for i in range(a.fixed_rounds):
-                fixed_round(agent, engine, rounds[(1 + i) % len(rounds)])
+                fixed_round(agent, engine, rounds[(1 + i) % len(rounds)], fixed_phases)
             torch.cuda.synchronize()
             f1 = dict(engine.stats)
         except RuntimeError as e:        # reported in the line, never a reason to lose the faithful number
@@ -497,6 +510,8 @@ def main():
                  "rows_per_step": round(fd["generated_tokens"] / max(1, fd["decode_steps"]), 2),
                  "decode_ms_per_step": round(1e3 * fd["decode_s"] / max(1, fd["decode_steps"]), 3),
                  "prefill_s_per_round": round(fd["prefill_s"] / a.fixed_rounds, 3),
+                 "decode_ms_per_step_by_phase": {k: round(1e3 * v[0] / max(1, v[1]), 3)
+                                                 for k, v in fixed_phases.items()},
                  "schedule": f"{MAX_RETRIES} batched attempts per phase, all {n_agents} rows forced to max_tokens"}
 
     # ---- ONE game, rows sharded over the replicas (latency half of SURVEY.md §8e)
@@ -532,6 +547,7 @@ def main():
         step_s = d["decode_s"] / max(1, steps)
         dec_ach = bytes_per_step / step_s / 1e9 if steps else 0.0
         pf_flops = d["prefill_tokens"] * cfg.prefill_gemm_flops_per_token() / a.tp   # per GPU
+        tf_sus = load_sustained_tf()
         line = {
             "metric": "agent_steps_per_sec", "value": round(total_agent_steps / dev_max, 4),
             "unit": "agent-steps/s", "n_gpus": world if world > 1 else a.tp, "steps": a.steps, "warmup": a.warmup,
@@ -551,7 +567,10 @@ def main():
                         "cached_tokens": int(d["cached_tokens"]), "seconds": round(d["prefill_s"], 3),
                         "achieved": round(pf_flops / max(1e-9, d["prefill_s"]) / 1e12, 1), "peak": tf_peak,
                         "unit": "TFLOP/s (GEMM flops / whole prefill time incl. attention, norms, sampling)",
-                        "frac": round(pf_flops / max(1e-9, d["prefill_s"]) / 1e12 / tf_peak, 4)},
+                        "frac": round(pf_flops / max(1e-9, d["prefill_s"]) / 1e12 / tf_peak, 4),
+                        "peak_kind": "burst (best of 10 cuBLAS launches)", "peak_sustained": tf_sus,
+                        "frac_of_sustained": (round(pf_flops / max(1e-9, d["prefill_s"]) / 1e12 / tf_sus, 4)
+                                              if tf_sus else None)},
             "value_mean_over_ranks": round(n_agents * a.steps * leaders * leaders / max(1e-9, sum(rank_dev)), 4),
             "ranks": {"device_s": rank_dev, "wall_s": rank_wall,
                       "note": "one independently seeded game per rank; value divides by the slowest rank"},

@@ -50,6 +50,7 @@ struct Gemm2Args {
   int epi;
   void* out;
   long long ld_out;
+  uint64_t hint_a, hint_b;   // L2 eviction priority of the activation / weight loads
 };
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -181,8 +182,8 @@ gemm2sm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
           uint8_t* sa = smem + stage * k2StageBytes;
           mbar_wait(&empty_bar[stage], phase ^ 1);
           if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2 * k2StageBytes);
-          tma_load_2d_2sm(sa, &tmap_a, &full_bar[stage], kb * k2BlockK, row_a, kEvictNormal);
-          tma_load_2d_2sm(sa + k2ABytes, &tmap_b, &full_bar[stage], kb * k2BlockK, row_b, kEvictLast);
+          tma_load_2d_2sm(sa, &tmap_a, &full_bar[stage], kb * k2BlockK, row_a, args.hint_a);
+          tma_load_2d_2sm(sa + k2ABytes, &tmap_b, &full_bar[stage], kb * k2BlockK, row_b, args.hint_b);
           if (++stage == k2Stages) {
             stage = 0;
             phase ^= 1;
@@ -330,6 +331,11 @@ int gemm2sm_bf16_tn(const void* X, const void* W, void* out, int M, int N, int K
   static const int group = getenv("BCG_GEMM_2SM_GROUP") ? atoi(getenv("BCG_GEMM_2SM_GROUP")) : 12;   // tuning knobs
   static const int stages = getenv("BCG_GEMM_2SM_STAGES") ? atoi(getenv("BCG_GEMM_2SM_STAGES")) : 7;
   a.group_m = a.tiles_m < group ? a.tiles_m : group;
+  static const int ha = getenv("BCG_GEMM_2SM_HINT_A") ? atoi(getenv("BCG_GEMM_2SM_HINT_A")) : 0;
+  static const int hb = getenv("BCG_GEMM_2SM_HINT_B") ? atoi(getenv("BCG_GEMM_2SM_HINT_B")) : 2;
+  const uint64_t hints[3] = {kEvictNormal, kEvictFirst, kEvictLast};
+  a.hint_a = hints[ha < 0 || ha > 2 ? 0 : ha];
+  a.hint_b = hints[hb < 0 || hb > 2 ? 2 : hb];
   a.epi = epi;
   a.out = out;
   a.ld_out = ld_out;

@@ -146,10 +146,16 @@ def main():
             w = torch.randn(N, K, device=DEV, dtype=torch.bfloat16) * 0.02
             x = torch.randn(M, K, device=DEV, dtype=torch.bfloat16)
             y = torch.empty(M, N, device=DEV, dtype=torch.bfloat16)
-            t_cublas = graph_time(lambda i: torch.matmul(x, w.t(), out=y), 1, inner=5)
-            t_ours = graph_time(lambda i: L.gemm(x, w, y, L.EPI_BF16), 1, inner=5)
+            # power-capped clocks drift over the ~0.1 s each arm runs, so the arms are interleaved
+            # (cuBLAS, ours, ours, cuBLAS) and each reports its mean
+            f_c = lambda i: torch.matmul(x, w.t(), out=y)
+            f_o = lambda i: L.gemm(x, w, y, L.EPI_BF16)
+            tc1, to1 = graph_time(f_c, 1, inner=5), graph_time(f_o, 1, inner=5)
+            to2, tc2 = graph_time(f_o, 1, inner=5), graph_time(f_c, 1, inner=5)
+            t_cublas, t_ours = 0.5 * (tc1 + tc2), 0.5 * (to1 + to2)
             fl = 2.0 * M * N * K
             out[name] = {"N": N, "K": K, "cublas_us": round(t_cublas, 1), "bcg_us": round(t_ours, 1),
+                         "order": "cublas, bcg, bcg, cublas", "runs_us": [round(v, 1) for v in (tc1, to1, to2, tc2)],
                          "bcg_over_cublas": round(t_ours / t_cublas, 3),
                          "cublas_TFLOPs": round(fl / t_cublas / 1e6, 0), "bcg_TFLOPs": round(fl / t_ours / 1e6, 0)}
             del w, x, y
