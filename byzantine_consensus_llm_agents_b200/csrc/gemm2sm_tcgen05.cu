@@ -331,11 +331,15 @@ int gemm2sm_bf16_tn(const void* X, const void* W, void* out, int M, int N, int K
   static const int group = getenv("BCG_GEMM_2SM_GROUP") ? atoi(getenv("BCG_GEMM_2SM_GROUP")) : 12;   // tuning knobs
   static const int stages = getenv("BCG_GEMM_2SM_STAGES") ? atoi(getenv("BCG_GEMM_2SM_STAGES")) : 7;
   a.group_m = a.tiles_m < group ? a.tiles_m : group;
-  static const int ha = getenv("BCG_GEMM_2SM_HINT_A") ? atoi(getenv("BCG_GEMM_2SM_HINT_A")) : 0;
-  static const int hb = getenv("BCG_GEMM_2SM_HINT_B") ? atoi(getenv("BCG_GEMM_2SM_HINT_B")) : 2;
+  // In this raster a group's activation panel (group_m x 256 rows) is what every wave of the group
+  // re-reads, a weight tile is shared by the group's m-tiles within ONE wave and then dead: keep the
+  // panel (evict-last), let the weights pass (normal).  Measured over a 14B layer at 12,390 tokens:
+  // 1,355 TFLOP/s vs 1,314-1,329 with the hints the other way round (weights evict-first: 1,245).
+  static const int ha = getenv("BCG_GEMM_2SM_HINT_A") ? atoi(getenv("BCG_GEMM_2SM_HINT_A")) : 2;
+  static const int hb = getenv("BCG_GEMM_2SM_HINT_B") ? atoi(getenv("BCG_GEMM_2SM_HINT_B")) : 0;
   const uint64_t hints[3] = {kEvictNormal, kEvictFirst, kEvictLast};
-  a.hint_a = hints[ha < 0 || ha > 2 ? 0 : ha];
-  a.hint_b = hints[hb < 0 || hb > 2 ? 2 : hb];
+  a.hint_a = hints[ha < 0 || ha > 2 ? 2 : ha];
+  a.hint_b = hints[hb < 0 || hb > 2 ? 0 : hb];
   a.epi = epi;
   a.out = out;
   a.ld_out = ld_out;
