@@ -109,7 +109,7 @@ decode_attn_kernel(const __grid_constant__ CUtensorMap kv_map, const __nv_bfloat
   __shared__ uint64_t full_bar[kAttnStages];
   __shared__ uint64_t empty_bar[kAttnStages];
   // per-warp partial outputs reuse the ring once every page has been consumed (keeps the CTA at
-  // 65 KB of shared memory -> 3 CTAs per SM)
+  // 51 KB of shared memory -> 4 CTAs per SM)
   float (*sm_acc)[G][128] = reinterpret_cast<float (*)[G][128]>(ring);
   __shared__ float sm_m[kAttnConsumers][G];
   __shared__ float sm_l[kAttnConsumers][G];

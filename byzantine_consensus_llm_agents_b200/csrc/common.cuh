@@ -16,7 +16,7 @@ enum : int {
   BCG_ERR_ARG = 1,       // bad argument (shape / alignment / null)
   BCG_ERR_CUDA = 2,      // a CUDA runtime / driver call failed
   BCG_ERR_UNSUPPORTED = 3,
-  BCG_ERR_TOO_LARGE = 4, // exceeds a compiled-in maximum
+  BCG_ERR_TOO_LARGE = 4, // exceeds a compiled-in maximum (BCG_STATUS_TOO_LARGE in include/bcg_b200.h)
 };
 
 #define BCG_CUDA_CHECK(expr)                                   \
