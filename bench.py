@@ -230,14 +230,19 @@ def kernel_roofline(engine, B: int, hbm_peak: float, peak_kind: str):
     alg_bytes = N * K * 2 + B * K * 2 + (B * (N // 2) * 2 if splits == 1 else splits * B * N * 4)
     achieved = alg_bytes / (ms * 1e-3) / 1e9
     traffic, traffic_source = None, None
-    prof = ROOT / "profiles" / "r01_gemm_decode_traffic.json"
+    prof = ROOT / "profiles" / "r02_gemm_decode_traffic.json"
     if prof.exists():
         try:
-            traffic = json.loads(prof.read_text()).get("dram_bytes_per_launch")
-            traffic_source = ("profiles/r01_gemm_decode_traffic.json (one ncu --set full capture of this kernel "
+            pj = json.loads(prof.read_text())
+            # the capture is of the 14B shape (weights dominate: rows <= 16 share the tile width)
+            if (N, K) == tuple(pj.get("N_K", (34816, 5120))) and B <= 16:
+                traffic = pj.get("dram_bytes_per_launch")
+            traffic_source = ("profiles/r02_gemm_decode_traffic.json (one ncu --set full capture of this kernel "
                               "and shape, dram__bytes_read.sum + dram__bytes_write.sum; not re-measured in this run)")
         except Exception:
             traffic = None
+        if traffic is None:
+            traffic_source = None
     return {"kernel": f"gemm_tcgen05_kernel<BN={16 if B <= 16 else 32 if B <= 32 else 64 if B <= 64 else 128}> "
                       f"(decode gate_up: M={B}, N={N}, K={K}, splits={splits}"
                       f"{', back-to-back launches with programmatic dependent launch' if gflags else ''})",

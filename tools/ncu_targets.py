@@ -21,11 +21,13 @@ def main():
     dev = torch.device("cuda:0")
     w = Weights.random_init(cfg, dev)
     tk = get_tokenizer(cfg.family, cfg.vocab)
-    eng = Engine(cfg, w, tk, max_model_len=2048, max_rows=16, prefill_tokens=16384, kv_pages=1200,
+    eng = Engine(cfg, w, tk, max_model_len=2048, max_rows=16, prefill_tokens=16384, kv_pages=1400,
                  use_cuda_graph=False)
     rng = np.random.default_rng(0)
     lo, hi = tk.regular_range
-    prompts = [rng.integers(lo, hi, size=1770).tolist() for _ in range(7)]
+    n_rows = int(sys.argv[1]) if len(sys.argv) > 1 else 7          # e.g. `10 1600`: the bench's decode shape
+    n_tok = int(sys.argv[2]) if len(sys.argv) > 2 else 1770
+    prompts = [rng.integers(lo, hi, size=n_tok).tolist() for _ in range(n_rows)]
     res = eng.generate([Request("", None, 0.5, 5, prompt_ids=p) for p in prompts])
     torch.cuda.synchronize()
     print("ok", [len(r.token_ids) for r in res])
