@@ -34,6 +34,7 @@ import torch
 from . import grammar as G
 from . import lib as L
 from .model import ModelConfig, ModelHandle, Weights
+from .tokenizer import CachedEncoder
 
 PAGE = 16
 SPLIT_TOKENS = 256
@@ -292,6 +293,7 @@ class Engine:
                           decode_steps=0, generated_tokens=0, prefill_s=0.0, decode_s=0.0, host_s=0.0,
                           gpu_launches=0, h2d_bytes=0, d2h_bytes=0)
         self._capture_stream = torch.cuda.Stream(self.dev)
+        self._encode = CachedEncoder(tokenizer)    # retries resubmit identical prompts
         # parity tests: when set to a list, the logits of every step are appended (forces the
         # eager, graph-less decode loop)
         self.debug_logits: Optional[list] = None
@@ -386,7 +388,7 @@ class Engine:
         ids_list, cached, pages_of, hashes_of = [], [], [], []
         use_forced = any(q.forced is not None for q in reqs)
         for q in reqs:
-            ids = list(q.prompt_ids) if q.prompt_ids is not None else self.tk.encode(q.prompt, True)
+            ids = list(q.prompt_ids) if q.prompt_ids is not None else self._encode(q.prompt)
             if len(ids) + q.max_tokens > self.max_model_len:
                 raise L.BcgError(f"prompt ({len(ids)} tokens) + max_tokens ({q.max_tokens}) exceeds "
                                  f"max_model_len ({self.max_model_len})")

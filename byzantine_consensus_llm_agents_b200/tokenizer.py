@@ -248,6 +248,34 @@ class SyntheticTokenizer:
         return out
 
 
+class CachedEncoder:
+    """Prompt string -> token ids with a small FIFO memo.  The reference's retry rule resubmits
+    identical prompts (main.py:293-317, 386-440: up to three batched attempts per phase, then
+    per-agent loops), so within a round every prompt after its first submission is a hit and costs
+    a dict lookup instead of a 2-4 ms BPE pass.  The returned list is shared: callers must not
+    mutate it."""
+
+    def __init__(self, tokenizer, capacity: int = 512):
+        self.tk, self.capacity = tokenizer, max(1, capacity)
+        self._memo: dict = {}
+        self.hits = self.misses = 0
+
+    def __call__(self, prompt: str) -> list:
+        ids = self._memo.get(prompt)
+        if ids is not None:
+            self.hits += 1
+            return ids
+        self.misses += 1
+        ids = self.tk.encode(prompt, True)
+        if len(self._memo) >= self.capacity:
+            self._memo.pop(next(iter(self._memo)))       # oldest entry (dicts keep insertion order)
+        self._memo[prompt] = ids
+        return ids
+
+    def clear(self) -> None:
+        self._memo.clear()
+
+
 @lru_cache(maxsize=8)
 def get_tokenizer(family: str = "qwen3", vocab_size: int = 151936) -> SyntheticTokenizer:
     return SyntheticTokenizer(family, vocab_size)

@@ -169,6 +169,28 @@ def test_reference_prompts_tokenise_at_realistic_density():
     assert 1200 <= n <= 2300
 
 
+def test_cached_encoder_returns_the_tokenizers_ids_and_evicts_oldest_first():
+    """Retries resubmit identical prompts: the engine's prompt memo must be invisible in the ids."""
+    from byzantine_consensus_llm_agents_b200.tokenizer import CachedEncoder, get_tokenizer
+    tk = get_tokenizer("qwen3", 151936)
+    enc = CachedEncoder(tk, capacity=3)
+    prompts = [f"<|im_start|>user\nround {i}: propose a value /no_think<|im_end|>\n" for i in range(5)]
+    for p in prompts[:3]:
+        assert enc(p) == tk.encode(p, True)
+    assert (enc.hits, enc.misses) == (0, 3)
+    assert enc(prompts[0]) is enc(prompts[0]) and enc.hits == 2     # same shared list, no re-encode
+    enc(prompts[3])                                                  # evicts prompts[0], the oldest
+    assert enc.misses == 4
+    enc(prompts[1])
+    assert enc.hits == 3
+    enc(prompts[0])
+    assert enc.misses == 5 and enc(prompts[0]) == tk.encode(prompts[0], True)
+    m = get_tokenizer("mistral", 32768)
+    assert CachedEncoder(m)("hi")[0] == m.bos_id                     # add_special_tokens=True, like vLLM
+    enc.clear()
+    assert enc(prompts[1]) == tk.encode(prompts[1], True) and enc.misses == 6
+
+
 def test_gemm_weight_interleave_layout():
     import torch
     from byzantine_consensus_llm_agents_b200.model import interleave_gate_up
