@@ -11,6 +11,15 @@ on a CPU and restated where they do not:
   stop on EOS / stop ids / max_tokens; text = decode(ids, skip specials)
                                                     vLLM semantics; the reference strips the text
 
+Pinning status: the reference ships NO golden vectors, known-answer tests or
+fixtures for this path, and its own engine (vLLM, `requirements.txt:1`, un-pinned) cannot run in
+this container — against the reference's own outputs the oracle is therefore "parity unpinned".
+What it IS pinned against: the real third-party libraries vLLM delegates to, run here —
+transformers 5.5 (`Qwen3ForCausalLM` / `MistralForCausalLM`, fp32) for the forward, xgrammar 0.2.0
+for every mask, Random123's Philox known-answer vectors for the sampler's generator — and the
+unmodified reference game code for prompts, schemas, retries and transcripts (oracle/ref_harness.py).
+The same statement is in DESIGN.md §4.
+
 It is a backend for oracle/ref_harness.py's vllm shim.  Greedy generation is a deterministic
 function of (prompt, schema, max_tokens); identical requests are memoised, which is exact.
 Every generation also records, per step, the masked top-1 / top-2 logits so GPU parity tests
